@@ -1,0 +1,373 @@
+// rt_api.cu -- the C ABI (include/rt_api.h) over the kernels: context, scene upload, render, resolve, probes.
+// No CPU fallback: every entry point needs a CUDA device and fails with RT_ERR_CUDA otherwise.
+#include "rt_api.h"
+
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <chrono>
+#include <string>
+#include <vector>
+
+#include "rt_device.h"
+#include "rt_kernels.h"
+#include "rt_pack.h"
+
+namespace {
+
+std::string g_last_error;
+
+struct DeviceBuffer {
+  void *ptr = nullptr; size_t bytes = 0;
+  cudaError_t upload(const void *src, size_t n, cudaStream_t s) {
+    release();
+    bytes = n;
+    if (n == 0) { return cudaMalloc(&ptr, 16); }                 // keep pointers valid for empty tables
+    cudaError_t e = cudaMalloc(&ptr, n);
+    if (e != cudaSuccess) return e;
+    return cudaMemcpyAsync(ptr, src, n, cudaMemcpyHostToDevice, s);
+  }
+  cudaError_t reserve(size_t n) {
+    if (n <= bytes && ptr) return cudaSuccess;
+    release();
+    bytes = n;
+    return cudaMalloc(&ptr, n ? n : 16);
+  }
+  void release() { if (ptr) cudaFree(ptr); ptr = nullptr; bytes = 0; }
+};
+
+double now_ms() {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+template <class T>
+cudaError_t to_device(DeviceBuffer &b, const T *src, size_t count, cudaStream_t s) { return b.upload(src, count * sizeof(T), s); }
+
+}  // namespace
+
+struct rt_context {
+  int device = 0, sm_count = 0;
+  cudaStream_t own_stream = nullptr, stream = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  std::string error;
+  // scene
+  bool has_scene = false;
+  rtd::Scene scene{};
+  rtp::PackedScene packed;
+  DeviceBuffer b_ref_nodes, b_xforms, b_structs, b_struct_children, b_fast_nodes, b_spheres, b_planars, b_materials,
+      b_checkers, b_perlin_vec, b_perlin_perm, b_arena;
+  // rng
+  DeviceBuffer b_rng_mats, b_rng_states, b_counters;
+  uint64_t rng_seed = 0, rng_first = 0, rng_count = 0; bool rng_valid = false;
+  // scratch for rt_render (host-buffer path)
+  DeviceBuffer b_pixels, b_rgb8;
+  rtk::LaunchInfo last_launch{};
+};
+
+static int fail(rt_context *ctx, int code, const std::string &msg) {
+  g_last_error = msg;
+  if (ctx) ctx->error = msg;
+  return code;
+}
+static int cuda_fail(rt_context *ctx, cudaError_t e, const char *what) {
+  return fail(ctx, RT_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define RT_CUDA(ctx, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return cuda_fail(ctx, e_, #call); } while (0)
+
+extern "C" {
+
+const char *rt_last_error_string(const rt_context *ctx) { return ctx ? ctx->error.c_str() : g_last_error.c_str(); }
+
+int rt_context_create(int device_id, rt_context **out) {
+  if (!out) return fail(nullptr, RT_ERR_INVALID, "rt_context_create: out is NULL");
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0)
+    return fail(nullptr, RT_ERR_CUDA, std::string("rt_context_create: no CUDA device (") + cudaGetErrorString(e) + "); this library has no CPU fallback");
+  if (device_id < 0 || device_id >= n) return fail(nullptr, RT_ERR_INVALID, "rt_context_create: device id out of range");
+  RT_CUDA(nullptr, cudaSetDevice(device_id));
+  rt_context *ctx = new rt_context();
+  ctx->device = device_id;
+  cudaDeviceProp prop;
+  e = cudaGetDeviceProperties(&prop, device_id);
+  if (e != cudaSuccess) { delete ctx; return cuda_fail(nullptr, e, "cudaGetDeviceProperties"); }
+  ctx->sm_count = prop.multiProcessorCount;
+  e = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) { delete ctx; return cuda_fail(nullptr, e, "cudaStreamCreate"); }
+  ctx->stream = ctx->own_stream;
+  for (int i = 0; i < 4; ++i) cudaEventCreate(&ctx->ev[i]);
+  std::vector<uint32_t> mats;
+  rtp::xorwow_sequence_matrices(mats);
+  e = ctx->b_rng_mats.upload(mats.data(), mats.size() * sizeof(uint32_t), ctx->stream);
+  if (e == cudaSuccess) e = ctx->b_counters.reserve(2 * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+  if (e != cudaSuccess) { rt_context_destroy(ctx); return cuda_fail(nullptr, e, "rt_context_create upload"); }
+  *out = ctx;
+  return RT_OK;
+}
+
+void rt_context_destroy(rt_context *ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  DeviceBuffer *all[] = {&ctx->b_ref_nodes, &ctx->b_xforms, &ctx->b_structs, &ctx->b_struct_children, &ctx->b_fast_nodes,
+                         &ctx->b_spheres, &ctx->b_planars, &ctx->b_materials, &ctx->b_checkers, &ctx->b_perlin_vec,
+                         &ctx->b_perlin_perm, &ctx->b_arena, &ctx->b_rng_mats, &ctx->b_rng_states, &ctx->b_counters,
+                         &ctx->b_pixels, &ctx->b_rgb8};
+  for (DeviceBuffer *b : all) b->release();
+  for (int i = 0; i < 4; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+  if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+  delete ctx;
+}
+
+int rt_context_set_stream(rt_context *ctx, void *cuda_stream) {
+  if (!ctx) return fail(nullptr, RT_ERR_INVALID, "rt_context_set_stream: ctx is NULL");
+  ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+  return RT_OK;
+}
+
+int rt_synchronize(rt_context *ctx) {
+  if (!ctx) return fail(nullptr, RT_ERR_INVALID, "rt_synchronize: ctx is NULL");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return RT_OK;
+}
+
+int rt_scene_upload(rt_context *ctx, const rt_scene_desc *desc, uint32_t traversal) {
+  if (!ctx || !desc) return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: NULL argument");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  ctx->has_scene = false;
+  ctx->packed = rtp::PackedScene();
+  rtp::PackedScene &p = ctx->packed;
+  int rc = rtp::pack_scene(*desc, traversal, p);
+  if (rc != RT_OK) return fail(ctx, rc, p.error);
+  cudaStream_t s = ctx->stream;
+#define UP(buf, vec) RT_CUDA(ctx, ctx->buf.upload((vec).data(), (vec).size() * sizeof((vec)[0]), s))
+  UP(b_ref_nodes, p.ref_nodes); UP(b_xforms, p.xforms); UP(b_structs, p.structures); UP(b_struct_children, p.struct_children);
+  UP(b_fast_nodes, p.fast_nodes); UP(b_spheres, p.spheres); UP(b_planars, p.planars); UP(b_materials, p.materials);
+  UP(b_checkers, p.checkers); UP(b_perlin_vec, p.perlin_vectors); UP(b_perlin_perm, p.perlin_perm); UP(b_arena, p.tex_arena);
+#undef UP
+  RT_CUDA(ctx, cudaStreamSynchronize(s));       // the host vectors may be reused after return
+  rtd::Scene &sc = ctx->scene;
+  sc.ref_nodes = (const float4 *)ctx->b_ref_nodes.ptr; sc.xforms = (const float4 *)ctx->b_xforms.ptr;
+  sc.structures = (const uint2 *)ctx->b_structs.ptr; sc.struct_children = (const uint32_t *)ctx->b_struct_children.ptr;
+  sc.ref_root = p.ref_root; sc.fast_nodes = (const float4 *)ctx->b_fast_nodes.ptr; sc.fast_root = p.fast_root;
+  sc.spheres = (const float4 *)ctx->b_spheres.ptr; sc.planars = (const float4 *)ctx->b_planars.ptr;
+  sc.sphere_count = p.sphere_count; sc.planar_count = p.planar_count;
+  sc.materials = (const uint4 *)ctx->b_materials.ptr; sc.checkers = (const float4 *)ctx->b_checkers.ptr;
+  sc.perlin_vectors = (const float4 *)ctx->b_perlin_vec.ptr; sc.perlin_perm = (const uint8_t *)ctx->b_perlin_perm.ptr;
+  sc.perlin_tables = p.perlin_tables; sc.tex_arena = (const uint8_t *)ctx->b_arena.ptr; sc.tex_bytes = p.tex_arena.size();
+  ctx->has_scene = true;
+  return RT_OK;
+}
+
+static int check_params(rt_context *ctx, const rt_render_params *p, int *row0, int *row1) {
+  if (!ctx || !p) return fail(ctx, RT_ERR_INVALID, "rt_render: NULL argument");
+  if (!ctx->has_scene) return fail(ctx, RT_ERR_NO_SCENE, "rt_render: no scene uploaded");
+  if (p->img_width <= 0 || p->img_height <= 0) return fail(ctx, RT_ERR_INVALID, "rt_render: image size must be positive");
+  if ((int64_t)p->img_width * p->img_height > 0x7fffffffLL / 3) return fail(ctx, RT_ERR_UNSUPPORTED, "rt_render: image too large");
+  if (p->max_bounces < 0 || p->max_bounces > 255)
+    return fail(ctx, RT_ERR_UNSUPPORTED, "rt_render: max_bounces must be 0..255 (the reference's bounce stack counter is a u8)");
+  int r0 = p->row_begin, r1 = p->row_end;
+  if (r0 == 0 && r1 == 0) r1 = p->img_height;
+  if (r0 < 0 || r1 > p->img_height || r0 >= r1) return fail(ctx, RT_ERR_INVALID, "rt_render: bad row range");
+  *row0 = r0; *row1 = r1;
+  return RT_OK;
+}
+
+int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels, rt_stats *stats) {
+  int row0, row1;
+  int rc = check_params(ctx, p, &row0, &row1);
+  if (rc != RT_OK) return rc;
+  if (!d_pixels) return fail(ctx, RT_ERR_INVALID, "rt_render_device: d_pixels_rgb is NULL");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t s = ctx->stream;
+  const uint64_t first_pixel = (uint64_t)row0 * p->img_width, count = (uint64_t)(row1 - row0) * p->img_width;
+  const uint64_t first_sub = first_pixel + p->subsequence_offset;
+
+  uint32_t launches = 0;
+  if (stats) RT_CUDA(ctx, cudaEventRecord(ctx->ev[0], s));
+  const bool cached = ctx->rng_valid && ctx->rng_seed == p->seed && ctx->rng_first == first_sub && ctx->rng_count == count &&
+                      !(p->flags & RT_RENDER_NO_RNG_CACHE);
+  if (!cached) {
+    RT_CUDA(ctx, ctx->b_rng_states.reserve(count * 6 * sizeof(uint32_t)));
+    RT_CUDA(ctx, rtk::launch_rng_init(p->seed, first_sub, count, (const uint32_t *)ctx->b_rng_mats.ptr,
+                                      (uint32_t *)ctx->b_rng_states.ptr, s));
+    ctx->rng_seed = p->seed; ctx->rng_first = first_sub; ctx->rng_count = count; ctx->rng_valid = true;
+    ++launches;
+  }
+  if (stats) RT_CUDA(ctx, cudaEventRecord(ctx->ev[1], s));
+  RT_CUDA(ctx, cudaMemsetAsync(ctx->b_counters.ptr, 0, 2 * sizeof(unsigned long long), s));
+
+  rtd::RenderArgs a;
+  memset(&a, 0, sizeof(a));
+  a.scene = ctx->scene;
+  a.pixels = d_pixels;
+  a.rng_states = (const uint32_t *)ctx->b_rng_states.ptr;
+  a.counters = (unsigned long long *)ctx->b_counters.ptr;
+  a.img_width = p->img_width; a.img_height = p->img_height;
+  a.samples_per_pixel = p->samples_per_pixel; a.max_bounces = p->max_bounces;
+  a.first_pixel = (int32_t)first_pixel; a.pixel_count = (int32_t)count;
+  a.defocus_angle = p->defocus_angle;
+  memcpy(a.background, p->background, 12); memcpy(a.dv, p->pixel_delta_v, 12); memcpy(a.du, p->pixel_delta_u, 12);
+  memcpy(a.cam, p->camera_pos, 12); memcpy(a.ddu, p->defocus_disk_u, 12); memcpy(a.ddv, p->defocus_disk_v, 12);
+  memcpy(a.p00, p->pixel00, 12);
+  a.sample_scale = (p->flags & RT_RENDER_OUTPUT_SUM) ? 1.0f : 1.0f / (float)p->samples_per_pixel;   // rt.cu:1657
+  a.count_rays = (p->flags & RT_RENDER_COUNT_RAYS) ? 1u : 0u;
+  const int mode = ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? 1 : 0;
+  RT_CUDA(ctx, rtk::launch_render(a, mode, ctx->sm_count, s, &ctx->last_launch));
+  ++launches;
+  if (stats) {
+    RT_CUDA(ctx, cudaEventRecord(ctx->ev[2], s));
+    unsigned long long counters[2] = {0, 0};
+    RT_CUDA(ctx, cudaMemcpyAsync(counters, ctx->b_counters.ptr, sizeof(counters), cudaMemcpyDeviceToHost, s));
+    RT_CUDA(ctx, cudaStreamSynchronize(s));
+    float t_rng = 0, t_render = 0;
+    cudaEventElapsedTime(&t_rng, ctx->ev[0], ctx->ev[1]);
+    cudaEventElapsedTime(&t_render, ctx->ev[1], ctx->ev[2]);
+    memset(stats, 0, sizeof(*stats));
+    stats->rng_init_ms = t_rng; stats->render_ms = t_render;
+    stats->paths = count * (uint64_t)(p->samples_per_pixel > 0 ? p->samples_per_pixel : 0);
+    stats->rays = counters[1];
+    stats->kernel_launches = launches;
+    stats->traversal_used = ctx->packed.traversal_used;
+    stats->grid_blocks = ctx->last_launch.grid; stats->block_threads = ctx->last_launch.block;
+    stats->regs_per_thread = ctx->last_launch.regs; stats->blocks_per_sm = ctx->last_launch.blocks_per_sm;
+  }
+  return RT_OK;
+}
+
+int rt_resolve_device(rt_context *ctx, const float *d_pixels, uint64_t n_pixels, float scale, uint8_t *d_rgb8) {
+  if (!ctx || !d_pixels || !d_rgb8) return fail(ctx, RT_ERR_INVALID, "rt_resolve_device: NULL argument");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  RT_CUDA(ctx, rtk::launch_resolve(d_pixels, n_pixels, scale, d_rgb8, ctx->stream));
+  return RT_OK;
+}
+
+int rt_render(rt_context *ctx, const rt_render_params *p, float *h_pixels, uint8_t *h_rgb8, rt_stats *stats) {
+  int row0, row1;
+  int rc = check_params(ctx, p, &row0, &row1);
+  if (rc != RT_OK) return rc;
+  const double t0 = now_ms();
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  const uint64_t n = (uint64_t)p->img_width * p->img_height;
+  RT_CUDA(ctx, ctx->b_pixels.reserve(n * 3 * sizeof(float)));
+  RT_CUDA(ctx, ctx->b_rgb8.reserve(n * 3 + 16));
+  if (row1 - row0 != p->img_height) RT_CUDA(ctx, cudaMemsetAsync(ctx->b_pixels.ptr, 0, n * 3 * sizeof(float), ctx->stream));
+  rt_stats local;
+  rc = rt_render_device(ctx, p, (float *)ctx->b_pixels.ptr, &local);
+  if (rc != RT_OK) return rc;
+  cudaStream_t s = ctx->stream;
+  float t_resolve = 0;
+  if (h_rgb8) {
+    RT_CUDA(ctx, cudaEventRecord(ctx->ev[2], s));
+    RT_CUDA(ctx, rtk::launch_resolve((const float *)ctx->b_pixels.ptr, n, 1.0f, (uint8_t *)ctx->b_rgb8.ptr, s));
+    RT_CUDA(ctx, cudaEventRecord(ctx->ev[3], s));
+    local.kernel_launches++;
+  }
+  const double t1 = now_ms();
+  if (h_rgb8) RT_CUDA(ctx, cudaMemcpyAsync(h_rgb8, ctx->b_rgb8.ptr, n * 3, cudaMemcpyDeviceToHost, s));
+  if (h_pixels) RT_CUDA(ctx, cudaMemcpyAsync(h_pixels, ctx->b_pixels.ptr, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, s));
+  RT_CUDA(ctx, cudaStreamSynchronize(s));
+  const double t2 = now_ms();
+  if (h_rgb8) cudaEventElapsedTime(&t_resolve, ctx->ev[2], ctx->ev[3]);
+  if (stats) {
+    *stats = local;
+    stats->resolve_ms = t_resolve; stats->d2h_ms = t2 - t1; stats->total_ms = t2 - t0;
+  }
+  return RT_OK;
+}
+
+// ---- probes ------------------------------------------------------------------------------------------
+
+int rt_probe_trace(rt_context *ctx, uint64_t n, const float *origins, const float *directions, const float *times,
+                   float tmin, float tmax, rt_probe_hit *out) {
+  if (!ctx || !origins || !directions || !out) return fail(ctx, RT_ERR_INVALID, "rt_probe_trace: NULL argument");
+  if (!ctx->has_scene) return fail(ctx, RT_ERR_NO_SCENE, "rt_probe_trace: no scene uploaded");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t s = ctx->stream;
+  DeviceBuffer o, d, t, r;
+  RT_CUDA(ctx, to_device(o, origins, 3 * n, s)); RT_CUDA(ctx, to_device(d, directions, 3 * n, s));
+  if (times) RT_CUDA(ctx, to_device(t, times, n, s));
+  RT_CUDA(ctx, r.reserve(n * sizeof(rt_probe_hit)));
+  const int mode = ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? 1 : 0;
+  cudaError_t e = rtk::launch_probe_trace(ctx->scene, mode, n, (const float *)o.ptr, (const float *)d.ptr,
+                                          times ? (const float *)t.ptr : nullptr, tmin, tmax, (rt_probe_hit *)r.ptr, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(out, r.ptr, n * sizeof(rt_probe_hit), cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  o.release(); d.release(); t.release(); r.release();
+  if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_probe_trace");
+  return RT_OK;
+}
+
+int rt_probe_scatter(rt_context *ctx, uint64_t n, const uint32_t *material6, const float *dir_in, const rt_probe_hit *rec,
+                     const float *unit_vec, const float *random_test, float *dir_out, float *atten_out, int32_t *scattered) {
+  if (!ctx || !material6 || !dir_in || !rec || !unit_vec || !random_test || !dir_out || !atten_out || !scattered)
+    return fail(ctx, RT_ERR_INVALID, "rt_probe_scatter: NULL argument");
+  if (!ctx->has_scene) return fail(ctx, RT_ERR_NO_SCENE, "rt_probe_scatter: no scene uploaded");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t s = ctx->stream;
+  // materials are packed exactly as rt_scene_upload packs them (same pre-resolution), against a scratch scene
+  std::vector<uint4> mats(2 * n);
+  rtp::PackedScene scratch;
+  scratch.checkers = ctx->packed.checkers; scratch.checker_ids = ctx->packed.checker_ids;
+  scratch.noise_ids = ctx->packed.noise_ids; scratch.perlin_tables = ctx->packed.perlin_tables;
+  const uint8_t *arena = ctx->packed.tex_arena.data();
+  for (uint64_t i = 0; i < n; ++i) {
+    rt_material m; memcpy(&m, material6 + 6 * i, sizeof(m));
+    rtp::pack_material(m, arena, ctx->packed.tex_arena.size(), scratch, &mats[2 * i]);
+    const uint32_t kind = (mats[2 * i].x >> 8) & 0xffu;
+    const bool known = (kind != rtd::TK_CHECKER_SOLID || mats[2 * i].z < ctx->packed.checkers.size() / 2) &&
+                       (kind != rtd::TK_NOISE || mats[2 * i].z < ctx->packed.perlin_tables);
+    if (!known) mats[2 * i].x = (mats[2 * i].x & ~0xff00u) | (rtd::TK_ARENA << 8);   // not in the uploaded tables: arena walk
+  }
+  DeviceBuffer bm, bd, br, bu, bt, od, oa, os;
+  RT_CUDA(ctx, to_device(bm, mats.data(), 2 * n, s)); RT_CUDA(ctx, to_device(bd, dir_in, 3 * n, s));
+  RT_CUDA(ctx, to_device(br, rec, n, s)); RT_CUDA(ctx, to_device(bu, unit_vec, 3 * n, s)); RT_CUDA(ctx, to_device(bt, random_test, n, s));
+  RT_CUDA(ctx, od.reserve(12 * n)); RT_CUDA(ctx, oa.reserve(12 * n)); RT_CUDA(ctx, os.reserve(4 * n));
+  cudaError_t e = rtk::launch_probe_scatter(ctx->scene, n, (const uint4 *)bm.ptr, (const float *)bd.ptr, (const rt_probe_hit *)br.ptr,
+                                            (const float *)bu.ptr, (const float *)bt.ptr, (float *)od.ptr, (float *)oa.ptr,
+                                            (int32_t *)os.ptr, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(dir_out, od.ptr, 12 * n, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(atten_out, oa.ptr, 12 * n, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(scattered, os.ptr, 4 * n, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  DeviceBuffer *all[] = {&bm, &bd, &br, &bu, &bt, &od, &oa, &os};
+  for (DeviceBuffer *b : all) b->release();
+  if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_probe_scatter");
+  return RT_OK;
+}
+
+int rt_probe_texture(rt_context *ctx, uint64_t n, uint64_t texture_offset, const float *uv, const float *points, float *rgb_out) {
+  if (!ctx || !uv || !points || !rgb_out) return fail(ctx, RT_ERR_INVALID, "rt_probe_texture: NULL argument");
+  if (!ctx->has_scene) return fail(ctx, RT_ERR_NO_SCENE, "rt_probe_texture: no scene uploaded");
+  if (texture_offset + sizeof(rt_texture) > ctx->packed.tex_arena.size()) return fail(ctx, RT_ERR_INVALID, "rt_probe_texture: offset out of range");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t s = ctx->stream;
+  DeviceBuffer bu, bp, bo;
+  RT_CUDA(ctx, to_device(bu, uv, 2 * n, s)); RT_CUDA(ctx, to_device(bp, points, 3 * n, s)); RT_CUDA(ctx, bo.reserve(12 * n));
+  cudaError_t e = rtk::launch_probe_texture(ctx->scene, n, (uint32_t)texture_offset, (const float *)bu.ptr, (const float *)bp.ptr, (float *)bo.ptr, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(rgb_out, bo.ptr, 12 * n, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  bu.release(); bp.release(); bo.release();
+  if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_probe_texture");
+  return RT_OK;
+}
+
+int rt_probe_xorwow(rt_context *ctx, uint64_t seed, uint64_t first_subsequence, uint64_t n, uint32_t *states6_out) {
+  if (!ctx || !states6_out) return fail(ctx, RT_ERR_INVALID, "rt_probe_xorwow: NULL argument");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  cudaStream_t s = ctx->stream;
+  DeviceBuffer b;
+  RT_CUDA(ctx, b.reserve(n * 24));
+  cudaError_t e = rtk::launch_rng_init(seed, first_subsequence, n, (const uint32_t *)ctx->b_rng_mats.ptr, (uint32_t *)b.ptr, s);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(states6_out, b.ptr, n * 24, cudaMemcpyDeviceToHost, s);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+  b.release();
+  if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_probe_xorwow");
+  return RT_OK;
+}
+
+}  // extern "C"

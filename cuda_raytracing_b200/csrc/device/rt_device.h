@@ -1,0 +1,94 @@
+// rt_device.h -- device-side scene layout shared by the host packer (rt_pack.cpp) and the kernels.
+//
+// The reference keeps one 120-byte AoS tagged union per object and reaches it through two dependent
+// indirections (u16 world ref -> u16 hittable ref -> struct; rt.cu:1127-1128, 1091).  Here every object
+// kind has its own array of 16-byte-aligned records read with 128-bit ld.global.nc, and every link is a
+// 32-bit TAGGED reference (kind in the top 3 bits, index below) resolved at pack time, so a stack pop
+// yields the kind without touching memory.
+#ifndef RT_DEVICE_H
+#define RT_DEVICE_H
+
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#include <vector_types.h>
+#else
+struct alignas(16) float4 { float x, y, z, w; };
+struct alignas(16) uint4 { unsigned x, y, z, w; };
+struct alignas(8) uint2 { unsigned x, y; };
+#endif
+
+namespace rtd {
+
+// tagged reference ------------------------------------------------------------------------------------
+enum Kind : uint32_t {
+  K_SPHERE = 0, K_BVH = 1, K_TRIANGLE = 2, K_QUAD = 3, K_TRANSLATION = 4, K_YROTATION = 5, K_STRUCTURE = 6,
+  K_NONE = 7
+};
+constexpr uint32_t KIND_SHIFT = 29;
+constexpr uint32_t INDEX_MASK = (1u << KIND_SHIFT) - 1u;
+#if defined(__CUDACC__)
+#define RTD_HD __host__ __device__ __forceinline__
+#else
+#define RTD_HD inline
+#endif
+RTD_HD uint32_t make_ref(uint32_t kind, uint32_t index) { return (kind << KIND_SHIFT) | index; }
+RTD_HD uint32_t ref_kind(uint32_t r) { return r >> KIND_SHIFT; }
+RTD_HD uint32_t ref_index(uint32_t r) { return r & INDEX_MASK; }
+
+// material record: 2 x 16 B per primitive (prim id = sphere index, or sphere_count + planar index) -------
+enum MatType : uint32_t { M_LAMBERTIAN = 0, M_METAL = 1, M_DIELECTRIC = 2, M_DIFFUSE_LIGHT = 3 };   // rt.cu:79-84
+enum TexKind : uint32_t {
+  TK_SOLID = 0,          // colour inline in m1.xyz (pre-resolved at pack time)
+  TK_CHECKER_SOLID = 1,  // checker of two solid colours: record `aux` in the checker table
+  TK_NOISE = 2,          // Perlin table `aux`, scale in m1.w
+  TK_ARENA = 3           // anything else: walk the reference-format texture arena from `tex_offset`
+};
+// m0 = { type | tex_kind << 8 | needs_uv << 16, tex_offset, aux, 0 }
+// m1 = { albedo/colour xyz, fuzz | refraction index | noise scale }
+
+struct Scene {
+  // reference-order graph (RT_TRAVERSAL_REFERENCE)
+  const float4 *ref_nodes;      // 2 per BVH node: {x0,x1,y0,y1} {z0,z1, left ref, right ref} (refs as raw bits)
+  const float4 *xforms;         // 1 per wrapper: translation {ox,oy,oz, child ref}; y-rotation {sin,cos,0, child ref}
+  const uint2 *structures;      // {first child slot, count}
+  const uint32_t *struct_children;
+  uint32_t ref_root;            // tagged ref of the reference's root BVH node
+  // own BVH over world-space primitives (RT_TRAVERSAL_FAST): 4 x float4 per node
+  //   n0 = {c0.x0, c0.x1, c0.y0, c0.y1}  n1 = {c1.x0, c1.x1, c1.y0, c1.y1}
+  //   n2 = {c0.z0, c0.z1, c1.z0, c1.z1}  n3 = {child0 ref, child1 ref, 0, 0}
+  const float4 *fast_nodes;
+  uint32_t fast_root;
+  // primitives
+  const float4 *spheres;        // 2 per sphere: {cx,cy,cz,r} {mx,my,mz, flags (bit0: needs uv)}
+  const float4 *planars;        // 4 per quad/triangle: {n.xyz,d} {q.xyz,w.x} {v.xyz,w.y} {u.xyz,w.z}
+  uint32_t sphere_count, planar_count;
+  // second primitive set for flattened instances (FAST mode on scenes with wrappers) lives in the same arrays
+  const uint4 *materials;       // 2 x 16 B per primitive id
+  const float4 *checkers;       // 2 per record: {inv_scale, even.rgb} {0, odd.rgb}
+  const float4 *perlin_vectors; // 256 per noise table (xyz, 0)
+  const uint8_t *perlin_perm;   // 256 per noise table (perm_x; the reference hashes all axes with it)
+  uint32_t perlin_tables;
+  const uint8_t *tex_arena;     // reference-format arena (TK_ARENA fallback), 16-byte aligned copy
+  uint64_t tex_bytes;
+};
+
+struct RenderArgs {
+  Scene scene;
+  float *pixels;                // img_width*img_height*3 f32 (device)
+  const uint32_t *rng_states;   // 6 words per pixel of the rendered row range: {d, v0..v4}
+  unsigned long long *counters; // [0] next work item, [1] rays traced
+  int32_t img_width, img_height, samples_per_pixel, max_bounces;
+  int32_t first_pixel, pixel_count;   // rendered range (row_begin*W .. row_end*W)
+  float defocus_angle;
+  float background[3];
+  float dv[3], du[3], cam[3], ddu[3], ddv[3], p00[3];
+  float sample_scale;           // 1/spp, or 1 with RT_RENDER_OUTPUT_SUM
+  uint32_t count_rays;
+};
+
+constexpr int STACK_CAPACITY = 32;     // traversal stack entries per thread (shared memory, [slot][thread])
+constexpr int MAX_BOUNCE_STACK = 256;  // RayColorStack.max_count is a u8 in the reference (rt.cu:220)
+
+}  // namespace rtd
+#endif

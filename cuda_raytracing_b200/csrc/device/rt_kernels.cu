@@ -1,0 +1,406 @@
+// rt_kernels.cu -- the sm_100a kernels of the path-tracing hot path and their launchers.
+//
+//   render_kernel<MODE>   persistent path tracer: replaces cuda_calc (rt.cu:1543-1589) and ray_color (1334-1371)
+//   rng_init_kernel       XORWOW states for subsequence = pixel (+offset): replaces init_gpu_data (rt.cu:1591-1606)
+//   resolve_kernel        1/spp scale + gamma + clamp + 8-bit quantise: replaces the host loop of pixels_to_ppm (1419-1433)
+//   probe_* kernels       the same device functions on caller-supplied batches (parity tests through the C ABI)
+//
+// Design: one lane owns one pixel and generates its samples IN ORDER from the pixel's own
+// XORWOW state (that is what makes the reference's RNG stream reproducible), but a lane never waits for the
+// other 31 pixels of its warp: when its path ends it starts its next sample at once (path regeneration), and
+// when its pixel is finished it claims the next pixel from a global queue with one warp-aggregated atomic
+// (ballot + popc + shuffle).  The traversal stack lives in shared memory ([slot][thread], conflict-free), the
+// attenuation stack in thread-local memory, the accumulator in registers (one 12-byte store per pixel instead
+// of the reference's global read-modify-write per sample).
+#include "rt_kernels.h"
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rt_device.h"
+#include "rt_math.cuh"
+#include "rt_shade.cuh"
+#include "rt_trace.cuh"
+
+namespace rtk {
+using namespace rtm;
+using rtd::RenderArgs;
+using rtd::Scene;
+using rts::PerlinSmem;
+using rtt::Hit;
+using rtt::Ray;
+
+constexpr int RT_BLOCK = 128;
+constexpr int RT_MIN_BLOCKS = 5;
+
+__device__ __forceinline__ void stage_perlin(const Scene &sc, PerlinSmem *dst) {
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+    dst->vec[i] = __ldg(sc.perlin_vectors + i);
+    dst->perm[i] = __ldg(sc.perlin_perm + i);
+  }
+}
+
+template <int MODE>
+__device__ __forceinline__ bool trace(const Scene &sc, Ray &r, Hit &h, uint32_t *stk, int stride) {
+  const float inf = __uint_as_float(0x7f800000u);
+  if (MODE == 0) return rtt::trace_reference(sc, r, 0.001f, inf, h, stk, stride);
+  return rtt::trace_fast(sc, r, 0.001f, inf, h, stk, stride);
+}
+
+template <int MODE, int MAXB>
+__global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) render_kernel(const RenderArgs a) {
+  extern __shared__ __align__(16) uint32_t smem[];
+  const Scene &sc = a.scene;
+  uint32_t *stk = smem + threadIdx.x;
+  const int stride = blockDim.x;
+  PerlinSmem *perlin = nullptr;
+  if (sc.perlin_tables > 0) {
+    perlin = reinterpret_cast<PerlinSmem *>(smem + rtd::STACK_CAPACITY * blockDim.x);
+    stage_perlin(sc, perlin);
+    __syncthreads();
+  }
+  const unsigned lane = threadIdx.x & 31u;
+  const unsigned full = 0xffffffffu;
+
+  const V3 du = v3(a.du[0], a.du[1], a.du[2]), dv = v3(a.dv[0], a.dv[1], a.dv[2]);
+  const V3 cam = v3(a.cam[0], a.cam[1], a.cam[2]);
+  const V3 bg = v3(a.background[0], a.background[1], a.background[2]);
+  const int capacity = a.max_bounces & 255;            // RayColorStack.max_count is a u8 (rt.cu:220, 1596)
+
+  float att_r[MAXB], att_g[MAXB], att_b[MAXB];         // thread-local attenuation stack (unwound backwards)
+
+  int pix = -1;
+  bool exhausted = false, new_path = false;
+  int samples_left = 0, budget = 0, depth = 0;
+  Rng rng = {0, 0, 0, 0, 0, 0};
+  Ray ray; ray.o = cam; ray.d = cam; ray.time = 0.0f;
+  V3 base = cam, acc = v3(0.0f, 0.0f, 0.0f);
+  unsigned long long rays = 0;
+
+  for (;;) {
+    // ---- claim pixels for idle lanes: one atomic per warp ----
+    const bool want = (pix < 0) && !exhausted;
+    const unsigned m = __ballot_sync(full, want);
+    if (m) {
+      const int leader = __ffs(m) - 1;
+      unsigned long long first = 0;
+      if ((int)lane == leader) first = atomicAdd(a.counters, (unsigned long long)__popc(m));
+      first = __shfl_sync(full, first, leader);
+      if (want) {
+        const unsigned long long item = first + __popc(m & ((1u << lane) - 1u));
+        if (item < (unsigned long long)a.pixel_count) {
+          pix = a.first_pixel + (int)item;
+          const uint2 *st = reinterpret_cast<const uint2 *>(a.rng_states) + 3 * (size_t)item;
+          const uint2 s0 = __ldg(st), s1 = __ldg(st + 1), s2 = __ldg(st + 2);
+          rng.d = s0.x; rng.v0 = s0.y; rng.v1 = s1.x; rng.v2 = s1.y; rng.v3 = s2.x; rng.v4 = s2.y;
+          const int j = pix % a.img_width, i = (pix - j) / a.img_width;     // rt.cu:1561-1567
+          const float fi = (float)i, fj = (float)j;
+          base = v3(fadd(ffma(fj, du.x, fmul(fi, dv.x)), a.p00[0]), fadd(ffma(fj, du.y, fmul(fi, dv.y)), a.p00[1]),
+                    fadd(ffma(fj, du.z, fmul(fi, dv.z)), a.p00[2]));
+          acc = v3(0.0f, 0.0f, 0.0f);
+          samples_left = a.samples_per_pixel;
+          new_path = true;
+          if (samples_left <= 0) {                      // spp <= 0: the reference writes 0 * scale
+            float *out = a.pixels + 3 * (size_t)pix;
+            out[0] = 0.0f; out[1] = 0.0f; out[2] = 0.0f;
+            pix = -1;
+          }
+        } else {
+          exhausted = true;
+        }
+      }
+    }
+    if (!__any_sync(full, pix >= 0)) break;
+    if (pix < 0) continue;
+
+    // ---- (1) camera ray generation (rt.cu:1570-1578) ----
+    if (new_path) {
+      new_path = false;
+      V3 o = cam;
+      if (!(a.defocus_angle <= 0.0f)) {
+        float px, py; rng_unit_disk(rng, px, py);
+        o = v3(fadd(ffma(px, a.ddu[0], fmul(py, a.ddv[0])), cam.x), fadd(ffma(px, a.ddu[1], fmul(py, a.ddv[1])), cam.y),
+               fadd(ffma(px, a.ddu[2], fmul(py, a.ddv[2])), cam.z));
+      }
+      const float xo = fadd(rng_uniform(rng), -0.5f);
+      const float yo = fadd(rng_uniform(rng), -0.5f);
+      V3 d = vsub(base, o);
+      d = v3(ffma(xo, du.x, d.x), ffma(xo, du.y, d.y), ffma(xo, du.z, d.z));
+      d = v3(ffma(yo, dv.x, d.x), ffma(yo, dv.y, d.y), ffma(yo, dv.z, d.z));
+      ray.o = o; ray.d = d; ray.time = rng_uniform(rng);
+      budget = capacity; depth = 0;
+    }
+
+    // ---- (2) one bounce: closest hit, (3) emission + scatter ----
+    V3 result = v3(0.0f, 0.0f, 0.0f);
+    bool done = (budget <= 0);
+    if (!done) {
+      ++rays;
+      Hit h; h.u = 0.0f; h.v = 0.0f; h.t = 0.0f; h.prim = 0; h.front = 0; h.p = cam; h.n = cam;
+      if (trace<MODE>(sc, ray, h, stk, stride)) {
+        const uint4 m0 = __ldg(sc.materials + 2 * h.prim);
+        const float4 m1 = __ldg(reinterpret_cast<const float4 *>(sc.materials + 2 * h.prim + 1));
+        const V3 U = rng_unit_vector(rng);               // rt.cu:500-501: drawn for EVERY hit, whatever the material
+        const float rtest = rng_uniform(rng);
+        V3 dout, att;
+        if (rts::scatter(sc, m0, m1, ray.d, h, U, rtest, perlin, dout, att)) {
+          ray.o = h.p; ray.d = dout;
+          if (depth != capacity) { att_r[depth] = att.x; att_g[depth] = att.y; att_b[depth] = att.z; ++depth; }
+          --budget;
+          done = (budget <= 0);                          // bounce budget spent: result stays (0,0,0) (Q14)
+        } else {
+          if ((m0.x & 0xffu) == rtd::M_DIFFUSE_LIGHT) result = rts::material_texture(sc, m0, m1, h, perlin);
+          done = true;
+        }
+      } else {
+        result = bg;
+        done = true;
+      }
+    }
+
+    // ---- (5) unwind, accumulate, resolve ----
+    if (done) {
+      while (depth > 0) {                                // result = att (.) result + emission, one fma per channel
+        --depth;
+        result = v3(ffma(result.x, att_r[depth], 0.0f), ffma(result.y, att_g[depth], 0.0f), ffma(result.z, att_b[depth], 0.0f));
+      }
+      acc = vadd(acc, result);
+      new_path = true;
+      if (--samples_left == 0) {
+        float *out = a.pixels + 3 * (size_t)pix;
+        out[0] = fmul(a.sample_scale, acc.x); out[1] = fmul(a.sample_scale, acc.y); out[2] = fmul(a.sample_scale, acc.z);
+        pix = -1;
+      }
+    }
+  }
+
+  if (a.count_rays) {                                    // warp-aggregated ray counter
+    for (int o = 16; o > 0; o >>= 1) rays += __shfl_xor_sync(full, rays, o);
+    if (lane == 0) atomicAdd(a.counters + 1, rays);
+  }
+}
+
+// ======================================================================================================
+// rng_init_kernel: XORWOW state after curand_init(seed, subsequence, 0) for a run of consecutive subsequences.
+// The state words v[0..4] are a 160-bit vector over GF(2); skipping s*2^67 steps multiplies it by
+// prod_k (M^(2^(67+k)))^(bit k of s).  One thread decomposes its first subsequence bit by bit, then walks
+// RNG_CHUNK-1 neighbours with the k=0 matrix staged in shared memory.  (cuRAND's own curand_init does the
+// same algebra with 2-bit windows and 218 KB of global tables per module.)
+// ======================================================================================================
+constexpr int RNG_CHUNK = 8;
+constexpr int RNG_BLOCK = 128;
+
+__device__ __forceinline__ void gf2_apply(const uint32_t *__restrict__ mat /* 160 x 5 */, uint32_t v[5]) {
+  uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    uint32_t bits = v[i];
+    while (bits) {
+      const int j = __ffs(bits) - 1;
+      bits &= bits - 1;
+      const uint32_t *row = mat + 5 * (i * 32 + j);
+      r0 ^= row[0]; r1 ^= row[1]; r2 ^= row[2]; r3 ^= row[3]; r4 ^= row[4];
+    }
+  }
+  v[0] = r0; v[1] = r1; v[2] = r2; v[3] = r3; v[4] = r4;
+}
+
+__global__ void __launch_bounds__(RNG_BLOCK) rng_init_kernel(uint64_t seed, uint64_t first, uint64_t n,
+                                                             const uint32_t *__restrict__ mats, uint32_t *__restrict__ out) {
+  __shared__ uint32_t m0[160 * 5];
+  for (int i = threadIdx.x; i < 160 * 5; i += blockDim.x) m0[i] = mats[i];
+  __syncthreads();
+  const uint64_t chunk = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t begin = chunk * RNG_CHUNK;
+  if (begin >= n) return;
+  // _curand_init_scratch (curand_kernel.h:772-790)
+  const uint32_t s0 = ((uint32_t)seed) ^ 0xaad26b49u;
+  const uint32_t s1 = (uint32_t)(seed >> 32) ^ 0xf7dcefddu;
+  const uint32_t t0 = 1099087573u * s0;
+  const uint32_t t1 = 2591861531u * s1;
+  const uint32_t d = 6615241u + t1 + t0;
+  uint32_t v[5] = {123456789u + t0, 362436069u ^ t0, 521288629u + t1, 88675123u ^ t1, 5783321u + t0};
+  uint64_t sub = first + begin;
+  for (int k = 0; sub; ++k, sub >>= 1)
+    if (sub & 1ull) gf2_apply(mats + (size_t)k * 800, v);
+  const uint64_t end = (begin + RNG_CHUNK < n) ? begin + RNG_CHUNK : n;
+  for (uint64_t i = begin; i < end; ++i) {
+    uint32_t *o = out + 6 * i;
+    o[0] = d; o[1] = v[0]; o[2] = v[1]; o[3] = v[2]; o[4] = v[3]; o[5] = v[4];
+    if (i + 1 < end) gf2_apply(m0, v);
+  }
+}
+
+cudaError_t launch_rng_init(uint64_t seed, uint64_t first_subsequence, uint64_t n, const uint32_t *seq_matrices,
+                            uint32_t *states_out, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  const uint64_t chunks = (n + RNG_CHUNK - 1) / RNG_CHUNK;
+  const unsigned grid = (unsigned)((chunks + RNG_BLOCK - 1) / RNG_BLOCK);
+  rng_init_kernel<<<grid, RNG_BLOCK, 0, stream>>>(seed, first_subsequence, n, seq_matrices, states_out);
+  return cudaGetLastError();
+}
+
+// ======================================================================================================
+// resolve_kernel: the accumulate -> resolve -> gamma tail (rt.cu:1586, 1391-1395, 1419-1427, utility.h:43-49).
+// HBM-bound streaming kernel: 12 B read + 3 B written per pixel, 4 channel values per thread (128-bit loads).
+// ======================================================================================================
+__device__ __forceinline__ uint8_t resolve_channel(float x, float scale) {
+  const float c = fmul(scale, x);
+  float g = (c > 0.0f) ? fsqrt(c) : 0.0f;                // linear_to_gamma; NaN -> 0
+  if (g < 0.0f) g = 0.0f;
+  if (g > 0.999f) g = 0.999f;
+  return (uint8_t)fmul(256.0f, g);
+}
+__global__ void __launch_bounds__(256) resolve_kernel(const float *__restrict__ px, uint64_t n_values, float scale,
+                                                      uint8_t *__restrict__ out) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const uint64_t quads = n_values / 4;
+  for (uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; q < quads; q += stride) {
+    const float4 v = __ldg(reinterpret_cast<const float4 *>(px) + q);
+    uchar4 o;
+    o.x = resolve_channel(v.x, scale); o.y = resolve_channel(v.y, scale);
+    o.z = resolve_channel(v.z, scale); o.w = resolve_channel(v.w, scale);
+    reinterpret_cast<uchar4 *>(out)[q] = o;
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n_values & 3)) {
+    const uint64_t i = quads * 4 + threadIdx.x;
+    out[i] = resolve_channel(px[i], scale);
+  }
+}
+cudaError_t launch_resolve(const float *pixels, uint64_t n_pixels, float scale, uint8_t *rgb8, cudaStream_t stream) {
+  const uint64_t n_values = 3 * n_pixels;
+  if (n_values == 0) return cudaSuccess;
+  uint64_t blocks = (n_values / 4 + 255) / 256;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks == 0) blocks = 1;
+  resolve_kernel<<<(unsigned)blocks, 256, 0, stream>>>(pixels, n_values, scale, rgb8);
+  return cudaGetLastError();
+}
+
+// ======================================================================================================
+// probe kernels: the device functions above on caller-supplied batches, one thread per item.
+// ======================================================================================================
+}  // namespace rtk
+#include "rt_api.h"
+namespace rtk {
+
+constexpr int PROBE_BLOCK = 128;
+
+template <int MODE>
+__global__ void __launch_bounds__(PROBE_BLOCK) probe_trace_kernel(const Scene sc, uint64_t n, const float *__restrict__ org,
+                                                                  const float *__restrict__ dir, const float *__restrict__ times,
+                                                                  float tmin, float tmax, rt_probe_hit *__restrict__ out) {
+  extern __shared__ __align__(16) uint32_t smem[];
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  Ray r;
+  r.o = v3(org[3 * i], org[3 * i + 1], org[3 * i + 2]);
+  r.d = v3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
+  r.time = times ? times[i] : 0.0f;
+  Hit h; h.u = 0.0f; h.v = 0.0f; h.t = 0.0f; h.prim = 0; h.front = 0; h.p = v3(0, 0, 0); h.n = v3(0, 0, 0);
+  bool hit;
+  if (MODE == 0) hit = rtt::trace_reference(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x);
+  else hit = rtt::trace_fast(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x);
+  rt_probe_hit o;
+  o.origin[0] = r.o.x; o.origin[1] = r.o.y; o.origin[2] = r.o.z;
+  o.direction[0] = r.d.x; o.direction[1] = r.d.y; o.direction[2] = r.d.z;
+  o.point[0] = h.p.x; o.point[1] = h.p.y; o.point[2] = h.p.z;
+  o.normal[0] = h.n.x; o.normal[1] = h.n.y; o.normal[2] = h.n.z;
+  o.t = h.t; o.u = h.u; o.v = h.v; o.hit = hit ? 1 : 0; o.front = h.front;
+  o.material_type = hit ? (int)(__ldg(sc.materials + 2 * h.prim).x & 0xffu) : -1;
+  out[i] = o;
+}
+
+__global__ void __launch_bounds__(PROBE_BLOCK) probe_scatter_kernel(const Scene sc, uint64_t n, const uint4 *__restrict__ mats,
+                                                                    const float *__restrict__ din, const rt_probe_hit *__restrict__ rec,
+                                                                    const float *__restrict__ uvec, const float *__restrict__ rtest,
+                                                                    float *__restrict__ dout, float *__restrict__ aout,
+                                                                    int32_t *__restrict__ scattered) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint4 m0 = mats[2 * i];
+  const uint4 m1u = mats[2 * i + 1];
+  const float4 m1 = make_float4(__uint_as_float(m1u.x), __uint_as_float(m1u.y), __uint_as_float(m1u.z), __uint_as_float(m1u.w));
+  Hit h;
+  h.p = v3(rec[i].point[0], rec[i].point[1], rec[i].point[2]);
+  h.n = v3(rec[i].normal[0], rec[i].normal[1], rec[i].normal[2]);
+  h.t = rec[i].t; h.u = rec[i].u; h.v = rec[i].v; h.front = rec[i].front; h.prim = 0;
+  V3 d = v3(0, 0, 0), a = v3(0, 0, 0);
+  const bool ok = rts::scatter(sc, m0, m1, v3(din[3 * i], din[3 * i + 1], din[3 * i + 2]), h,
+                               v3(uvec[3 * i], uvec[3 * i + 1], uvec[3 * i + 2]), rtest[i], nullptr, d, a);
+  dout[3 * i] = d.x; dout[3 * i + 1] = d.y; dout[3 * i + 2] = d.z;
+  aout[3 * i] = a.x; aout[3 * i + 1] = a.y; aout[3 * i + 2] = a.z;
+  scattered[i] = ok ? 1 : 0;
+}
+
+__global__ void __launch_bounds__(PROBE_BLOCK) probe_texture_kernel(const Scene sc, uint64_t n, uint32_t off,
+                                                                    const float *__restrict__ uv, const float *__restrict__ pts,
+                                                                    float *__restrict__ rgb) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const V3 c = rts::arena_texture(sc, off, uv[2 * i], uv[2 * i + 1], v3(pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]));
+  rgb[3 * i] = c.x; rgb[3 * i + 1] = c.y; rgb[3 * i + 2] = c.z;
+}
+
+static inline unsigned probe_grid(uint64_t n) { return (unsigned)((n + PROBE_BLOCK - 1) / PROBE_BLOCK); }
+
+cudaError_t launch_probe_trace(const rtd::Scene &scene, int mode, uint64_t n, const float *origins, const float *directions,
+                               const float *times, float tmin, float tmax, rt_probe_hit *out, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  const size_t smem = sizeof(uint32_t) * rtd::STACK_CAPACITY * PROBE_BLOCK;
+  if (mode == 0) probe_trace_kernel<0><<<probe_grid(n), PROBE_BLOCK, smem, stream>>>(scene, n, origins, directions, times, tmin, tmax, out);
+  else probe_trace_kernel<1><<<probe_grid(n), PROBE_BLOCK, smem, stream>>>(scene, n, origins, directions, times, tmin, tmax, out);
+  return cudaGetLastError();
+}
+cudaError_t launch_probe_scatter(const rtd::Scene &scene, uint64_t n, const uint4 *materials2, const float *dir_in,
+                                 const rt_probe_hit *rec, const float *unit_vec, const float *random_test, float *dir_out,
+                                 float *atten_out, int32_t *scattered, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  probe_scatter_kernel<<<probe_grid(n), PROBE_BLOCK, 0, stream>>>(scene, n, materials2, dir_in, rec, unit_vec, random_test,
+                                                                   dir_out, atten_out, scattered);
+  return cudaGetLastError();
+}
+cudaError_t launch_probe_texture(const rtd::Scene &scene, uint64_t n, uint32_t texture_offset, const float *uv,
+                                 const float *points, float *rgb_out, cudaStream_t stream) {
+  if (n == 0) return cudaSuccess;
+  probe_texture_kernel<<<probe_grid(n), PROBE_BLOCK, 0, stream>>>(scene, n, texture_offset, uv, points, rgb_out);
+  return cudaGetLastError();
+}
+
+// ======================================================================================================
+// launch_render: persistent grid = SMs x resident blocks per SM (occupancy API), so every SM is full and the
+// work queue does the load balancing.
+// ======================================================================================================
+template <int MODE, int MAXB>
+static cudaError_t launch_render_t(const RenderArgs &args, int sm_count, cudaStream_t stream, LaunchInfo *info) {
+  size_t smem = sizeof(uint32_t) * rtd::STACK_CAPACITY * RT_BLOCK;
+  if (args.scene.perlin_tables > 0) smem += sizeof(PerlinSmem);
+  auto kernel = render_kernel<MODE, MAXB>;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 50);
+  if (e != cudaSuccess) return e;
+  int per_sm = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, RT_BLOCK, smem);
+  if (e != cudaSuccess) return e;
+  if (per_sm < 1) per_sm = 1;
+  long long want = ((long long)args.pixel_count + RT_BLOCK - 1) / RT_BLOCK;
+  long long grid = (long long)sm_count * per_sm;
+  if (grid > want) grid = want;
+  if (grid < 1) grid = 1;
+  if (info) {
+    cudaFuncAttributes fa;
+    cudaFuncGetAttributes(&fa, kernel);
+    info->grid = (int)grid; info->block = RT_BLOCK; info->regs = fa.numRegs; info->blocks_per_sm = per_sm; info->smem = smem;
+  }
+  kernel<<<(unsigned)grid, RT_BLOCK, smem, stream>>>(args);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_render(const rtd::RenderArgs &args, int mode, int sm_count, cudaStream_t stream, LaunchInfo *info) {
+  const bool small = (args.max_bounces & 255) <= 64;
+  if (mode == 0) return small ? launch_render_t<0, 64>(args, sm_count, stream, info) : launch_render_t<0, 256>(args, sm_count, stream, info);
+  return small ? launch_render_t<1, 64>(args, sm_count, stream, info) : launch_render_t<1, 256>(args, sm_count, stream, info);
+}
+
+}  // namespace rtk

@@ -1,0 +1,419 @@
+// rt_pack.cpp -- host-side packer (product code, plain C++): turns the reference's flat scene arrays
+// (Hittable[120 B], u16 world refs, texture byte arena; rt.cu:1699-1733 uploads them verbatim) into the
+// device layout of rt_device.h: SoA primitive records, tagged 32-bit links, pre-resolved materials, Perlin
+// tables split out for shared-memory staging, and -- for RT_TRAVERSAL_FAST -- world-space flattened instances
+// under a SAH BVH with 64-byte two-child nodes.
+#include "rt_pack.h"
+
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+#include <map>
+
+namespace rtp {
+using namespace rtd;
+
+static inline float4 f4(float x, float y, float z, float w) { float4 r; r.x = x; r.y = y; r.z = z; r.w = w; return r; }
+static inline float as_float(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+static inline uint32_t as_uint(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+
+// ---------------------------------------------------------------------------------------- textures / materials
+static const rt_texture *tex_at(const uint8_t *arena, uint64_t bytes, uint64_t off) {
+  if (!arena || off + sizeof(rt_texture) > bytes) return nullptr;
+  return reinterpret_cast<const rt_texture *>(arena + off);
+}
+static bool tex_has_image(const uint8_t *arena, uint64_t bytes, uint64_t off, int depth = 0) {
+  const rt_texture *t = tex_at(arena, bytes, off);
+  if (!t || depth > 32) return false;
+  if (t->type == RT_TEX_IMAGE) return true;
+  if (t->type == RT_TEX_CHECKER)
+    return tex_has_image(arena, bytes, t->u.checker.even, depth + 1) || tex_has_image(arena, bytes, t->u.checker.odd, depth + 1);
+  return false;
+}
+
+
+void pack_material(const rt_material &m, const uint8_t *arena, uint64_t bytes, PackedScene &out, uint4 rec[2]) {
+  PackedScene &st = out;
+  uint32_t type = m.type, kind = TK_SOLID, tex_off = 0, aux = 0, needs_uv = 0;
+  float a = 0, b = 0, c = 0, d = 0;
+  if (type == RT_MAT_METAL) { a = m.u.metal.albedo.x; b = m.u.metal.albedo.y; c = m.u.metal.albedo.z; d = m.u.metal.fuzz; }
+  else if (type == RT_MAT_DIELECTRIC) { d = m.u.dielectric.refraction_index; }
+  else {
+    tex_off = (uint32_t)m.u.texture;
+    const rt_texture *t = tex_at(arena, bytes, m.u.texture);
+    kind = TK_ARENA;
+    if (t && t->type == RT_TEX_SOLID) {
+      kind = TK_SOLID; a = t->u.solid.albedo.x; b = t->u.solid.albedo.y; c = t->u.solid.albedo.z;
+    } else if (t && t->type == RT_TEX_CHECKER) {
+      const rt_texture *e = tex_at(arena, bytes, t->u.checker.even), *o = tex_at(arena, bytes, t->u.checker.odd);
+      if (e && o && e->type == RT_TEX_SOLID && o->type == RT_TEX_SOLID) {
+        kind = TK_CHECKER_SOLID;
+        auto it = st.checker_ids.find(m.u.texture);
+        if (it == st.checker_ids.end()) {
+          aux = (uint32_t)(out.checkers.size() / 2);
+          out.checkers.push_back(f4(t->u.checker.inverted_scale, e->u.solid.albedo.x, e->u.solid.albedo.y, e->u.solid.albedo.z));
+          out.checkers.push_back(f4(0.0f, o->u.solid.albedo.x, o->u.solid.albedo.y, o->u.solid.albedo.z));
+          st.checker_ids[m.u.texture] = aux;
+        } else aux = it->second;
+      }
+    } else if (t && t->type == RT_TEX_NOISE && t->u.noise.noise_offset + sizeof(rt_perlin) <= bytes) {
+      kind = TK_NOISE; d = t->u.noise.scale;
+      auto it = st.noise_ids.find(t->u.noise.noise_offset);
+      if (it == st.noise_ids.end()) {
+        aux = out.perlin_tables++;
+        const rt_perlin *pn = reinterpret_cast<const rt_perlin *>(arena + t->u.noise.noise_offset);
+        for (int i = 0; i < RT_PERLIN_POINTS; ++i) {
+          out.perlin_vectors.push_back(f4(pn->vectors[i].x, pn->vectors[i].y, pn->vectors[i].z, 0.0f));
+          out.perlin_perm.push_back((uint8_t)(pn->perm_x[i] & 255));   // a permutation of 0..255
+        }
+        st.noise_ids[t->u.noise.noise_offset] = aux;
+      } else aux = it->second;
+    }
+    if (kind == TK_ARENA) needs_uv = tex_has_image(arena, bytes, m.u.texture) ? 1u : 0u;
+  }
+  rec[0].x = type | (kind << 8) | (needs_uv << 16); rec[0].y = tex_off; rec[0].z = aux; rec[0].w = 0;
+  rec[1].x = as_uint(a); rec[1].y = as_uint(b); rec[1].z = as_uint(c); rec[1].w = as_uint(d);
+}
+
+// ---------------------------------------------------------------------------------------- geometry helpers (f32)
+struct V { float x, y, z; };
+static inline V vv(const rt_vec3 &a) { return V{a.x, a.y, a.z}; }
+struct Box { float lo[3], hi[3]; };
+static inline Box box_of(const rt_aabb &b) { return Box{{b.x0, b.y0, b.z0}, {b.x1, b.y1, b.z1}}; }
+static inline Box box_empty() { return Box{{INFINITY, INFINITY, INFINITY}, {-INFINITY, -INFINITY, -INFINITY}}; }
+static inline void box_grow(Box &b, const Box &o) {
+  for (int a = 0; a < 3; ++a) { b.lo[a] = std::min(b.lo[a], o.lo[a]); b.hi[a] = std::max(b.hi[a], o.hi[a]); }
+}
+static inline void box_point(Box &b, V p) {
+  b.lo[0] = std::min(b.lo[0], p.x); b.hi[0] = std::max(b.hi[0], p.x);
+  b.lo[1] = std::min(b.lo[1], p.y); b.hi[1] = std::max(b.hi[1], p.y);
+  b.lo[2] = std::min(b.lo[2], p.z); b.hi[2] = std::max(b.hi[2], p.z);
+}
+static inline float box_area(const Box &b) {
+  float dx = b.hi[0] - b.lo[0], dy = b.hi[1] - b.lo[1], dz = b.hi[2] - b.lo[2];
+  if (!(dx >= 0) || !(dy >= 0) || !(dz >= 0)) return 0.0f;
+  return 2.0f * (dx * dy + dy * dz + dz * dx);
+}
+// object -> world transform of a (translation o y-rotation)* chain: world = R(p) + T,
+// R: x = c*x' + s*z', z = -s*x' + c*z'   (the inverse of the ray rotation of rt.cu:1196-1206)
+struct Xf { float c = 1.0f, s = 0.0f; V t{0, 0, 0}; bool identity = true; };
+static inline V xf_dir(const Xf &x, V p) { return V{x.c * p.x + x.s * p.z, p.y, -x.s * p.x + x.c * p.z}; }
+static inline V xf_point(const Xf &x, V p) { V r = xf_dir(x, p); return V{r.x + x.t.x, r.y + x.t.y, r.z + x.t.z}; }
+
+struct Leaf { uint32_t ref; Box box; float centroid[3]; };
+
+// ---------------------------------------------------------------------------------------- SAH BVH (own traversal)
+struct SahBuilder {
+  std::vector<Leaf> &leaves;
+  std::vector<float4> &nodes;
+  uint32_t max_depth = 0;
+  explicit SahBuilder(std::vector<Leaf> &l, std::vector<float4> &n) : leaves(l), nodes(n) {}
+
+  // returns the tagged ref of the subtree over leaves[begin,end) and its box
+  uint32_t build(size_t begin, size_t end, uint32_t depth, Box &box_out) {
+    max_depth = std::max(max_depth, depth);
+    if (end - begin == 1) { box_out = leaves[begin].box; return leaves[begin].ref; }
+    size_t n = end - begin, best_split = begin + n / 2;
+    int best_axis = -1;
+    if (depth < 16) {                                  // full-sweep SAH; deeper levels fall back to a balanced median
+      float best_cost = INFINITY;
+      std::vector<float> right_area(n);
+      for (int axis = 0; axis < 3; ++axis) {
+        std::sort(leaves.begin() + begin, leaves.begin() + end,
+                  [axis](const Leaf &a, const Leaf &b) { return a.centroid[axis] < b.centroid[axis]; });
+        Box acc = box_empty();
+        for (size_t i = n; i-- > 1;) { box_grow(acc, leaves[begin + i].box); right_area[i] = box_area(acc); }
+        acc = box_empty();
+        for (size_t i = 1; i < n; ++i) {
+          box_grow(acc, leaves[begin + i - 1].box);
+          float cost = box_area(acc) * (float)i + right_area[i] * (float)(n - i);
+          if (cost < best_cost) { best_cost = cost; best_axis = axis; best_split = begin + i; }
+        }
+      }
+    }
+    if (best_axis < 0) {                               // median on the widest centroid axis
+      Box cb = box_empty();
+      for (size_t i = begin; i < end; ++i) box_point(cb, V{leaves[i].centroid[0], leaves[i].centroid[1], leaves[i].centroid[2]});
+      best_axis = 0;
+      for (int a = 1; a < 3; ++a) if (cb.hi[a] - cb.lo[a] > cb.hi[best_axis] - cb.lo[best_axis]) best_axis = a;
+      best_split = begin + n / 2;
+    }
+    const int axis = best_axis;
+    std::sort(leaves.begin() + begin, leaves.begin() + end,
+              [axis](const Leaf &a, const Leaf &b) { return a.centroid[axis] < b.centroid[axis]; });
+    const uint32_t me = (uint32_t)(nodes.size() / 4);
+    nodes.resize(nodes.size() + 4);
+    Box b0, b1;
+    const uint32_t r0 = build(begin, best_split, depth + 1, b0);
+    const uint32_t r1 = build(best_split, end, depth + 1, b1);
+    nodes[4 * me + 0] = f4(b0.lo[0], b0.hi[0], b0.lo[1], b0.hi[1]);
+    nodes[4 * me + 1] = f4(b1.lo[0], b1.hi[0], b1.lo[1], b1.hi[1]);
+    nodes[4 * me + 2] = f4(b0.lo[2], b0.hi[2], b1.lo[2], b1.hi[2]);
+    nodes[4 * me + 3] = f4(as_float(r0), as_float(r1), 0.0f, 0.0f);
+    box_out = b0; box_grow(box_out, b1);
+    return make_ref(K_BVH, me);
+  }
+};
+
+// ---------------------------------------------------------------------------------------- the packer proper
+namespace {
+
+struct Packer {
+  const rt_scene_desc &d;
+  PackedScene &out;
+  std::vector<uint32_t> tag;                    // hittable index -> tagged ref (reference graph)
+  std::vector<rt_material> sphere_mats, planar_mats;
+  std::vector<Leaf> leaves;                     // FAST traversal leaves
+  Packer(const rt_scene_desc &desc, PackedScene &o) : d(desc), out(o) {}
+
+  const rt_hittable &H(uint32_t i) const { return d.hittables[i]; }
+
+  uint32_t add_sphere(V c, V mv, float r, const rt_material &m) {
+    uint32_t idx = (uint32_t)(out.spheres.size() / 2);
+    uint32_t flags = 0;
+    if ((m.type == RT_MAT_LAMBERTIAN || m.type == RT_MAT_DIFFUSE_LIGHT) &&
+        tex_has_image(d.texture_arena, d.texture_bytes, m.u.texture)) flags |= 1u;
+    out.spheres.push_back(f4(c.x, c.y, c.z, r));
+    out.spheres.push_back(f4(mv.x, mv.y, mv.z, as_float(flags)));
+    sphere_mats.push_back(m);
+    return idx;
+  }
+  uint32_t add_planar(const rt_geometry &g, const rt_material &m) {
+    uint32_t idx = (uint32_t)(out.planars.size() / 4);
+    out.planars.push_back(f4(g.normal.x, g.normal.y, g.normal.z, g.d));
+    out.planars.push_back(f4(g.q.x, g.q.y, g.q.z, g.w.x));
+    out.planars.push_back(f4(g.v.x, g.v.y, g.v.z, g.w.y));
+    out.planars.push_back(f4(g.u.x, g.u.y, g.u.z, g.w.z));
+    planar_mats.push_back(m);
+    return idx;
+  }
+
+  // exact stack need of the reference-order traversal (see trace_reference): `base` = entries below this one
+  uint32_t stack_need(uint32_t href, uint32_t base, int guard) const {
+    if (guard > 64 || href >= d.hittable_count) return base;
+    const rt_hittable &h = H(href);
+    switch (h.type) {
+      case RT_OBJ_BVH_NODE: {
+        uint32_t l = d.world_refs[h.u.bvh.left], r = d.world_refs[h.u.bvh.right];
+        return std::max(base + 2, std::max(stack_need(l, base + 1, guard + 1), stack_need(r, base, guard + 1)));
+      }
+      case RT_OBJ_TRANSLATION: return std::max(base + 2, stack_need(h.u.translation.child, base + 1, guard + 1));
+      case RT_OBJ_Y_ROTATION: return std::max(base + 2, stack_need(h.u.y_rotation.child, base + 1, guard + 1));
+      case RT_OBJ_STRUCTURE: {
+        uint32_t need = base + (uint32_t)h.u.structure.count;
+        for (uint32_t k = 0; k < h.u.structure.count; ++k)
+          need = std::max(need, stack_need(h.u.structure.first + k, base + k, guard + 1));
+        return need;
+      }
+      default: return base;
+    }
+  }
+
+  // world-space copy of everything below `href` (FAST traversal)
+  void flatten(uint32_t href, const Xf &xf, int guard) {
+    if (guard > 64 || href >= d.hittable_count) return;
+    const rt_hittable &h = H(href);
+    switch (h.type) {
+      case RT_OBJ_SPHERE: {
+        Leaf lf;
+        if (xf.identity) { lf.ref = tag[href]; lf.box = box_of(h.u.sphere.bbox); }
+        else {
+          V c = xf_point(xf, vv(h.u.sphere.center)), mv = xf_dir(xf, vv(h.u.sphere.direction));
+          float r = h.u.sphere.radius, pad = 1e-4f * (1.0f + fabsf(r));
+          lf.ref = make_ref(K_SPHERE, add_sphere(c, mv, r, h.u.sphere.mat));
+          lf.box = box_empty();
+          for (int e = 0; e < 2; ++e) {
+            V p{c.x + e * mv.x, c.y + e * mv.y, c.z + e * mv.z};
+            box_point(lf.box, V{p.x - r - pad, p.y - r - pad, p.z - r - pad});
+            box_point(lf.box, V{p.x + r + pad, p.y + r + pad, p.z + r + pad});
+          }
+        }
+        push_leaf(lf);
+      } break;
+      case RT_OBJ_TRIANGLE: case RT_OBJ_QUAD: {
+        Leaf lf;
+        const bool tri = h.type == RT_OBJ_TRIANGLE;
+        if (xf.identity) { lf.ref = tag[href]; lf.box = box_of(h.u.planar.bbox); }
+        else {
+          rt_geometry g;
+          V q = xf_point(xf, vv(h.u.planar.geom.q)), u = xf_dir(xf, vv(h.u.planar.geom.u)), v = xf_dir(xf, vv(h.u.planar.geom.v));
+          V n{u.y * v.z - u.z * v.y, u.z * v.x - u.x * v.z, u.x * v.y - u.y * v.x};       // make_quad (rt.cu:604-620)
+          float nn = n.x * n.x + n.y * n.y + n.z * n.z, len = sqrtf(nn);
+          g.q = rt_vec3{q.x, q.y, q.z}; g.u = rt_vec3{u.x, u.y, u.z}; g.v = rt_vec3{v.x, v.y, v.z};
+          g.w = rt_vec3{n.x * (1.0f / nn), n.y * (1.0f / nn), n.z * (1.0f / nn)};
+          g.normal = len == 0.0f ? rt_vec3{0, 0, 0} : rt_vec3{n.x / len, n.y / len, n.z / len};
+          g.d = g.normal.x * q.x + g.normal.y * q.y + g.normal.z * q.z;
+          lf.ref = make_ref(tri ? K_TRIANGLE : K_QUAD, add_planar(g, h.u.planar.mat));
+          lf.box = box_empty();
+          box_point(lf.box, q); box_point(lf.box, V{q.x + u.x, q.y + u.y, q.z + u.z});
+          box_point(lf.box, V{q.x + v.x, q.y + v.y, q.z + v.z});
+          if (!tri) box_point(lf.box, V{q.x + u.x + v.x, q.y + u.y + v.y, q.z + u.z + v.z});
+          for (int a = 0; a < 3; ++a) {
+            float pad = 1e-3f + 1e-5f * std::max(fabsf(lf.box.lo[a]), fabsf(lf.box.hi[a]));
+            lf.box.lo[a] -= pad; lf.box.hi[a] += pad;
+          }
+        }
+        push_leaf(lf);
+      } break;
+      case RT_OBJ_TRANSLATION: {
+        Xf x = xf; V o = xf_dir(xf, vv(h.u.translation.offset));
+        x.t = V{xf.t.x + o.x, xf.t.y + o.y, xf.t.z + o.z}; x.identity = false;
+        flatten(h.u.translation.child, x, guard + 1);
+      } break;
+      case RT_OBJ_Y_ROTATION: {
+        Xf x = xf; float c2 = h.u.y_rotation.cos_theta, s2 = h.u.y_rotation.sin_theta;
+        x.c = xf.c * c2 - xf.s * s2; x.s = xf.s * c2 + xf.c * s2; x.identity = false;
+        flatten(h.u.y_rotation.child, x, guard + 1);
+      } break;
+      case RT_OBJ_STRUCTURE:
+        for (uint32_t k = 0; k < h.u.structure.count; ++k) flatten(h.u.structure.first + k, xf, guard + 1);
+        break;
+      default: break;
+    }
+  }
+  void push_leaf(Leaf lf) {
+    for (int a = 0; a < 3; ++a) lf.centroid[a] = 0.5f * (lf.box.lo[a] + lf.box.hi[a]);
+    leaves.push_back(lf);
+  }
+
+  int run(uint32_t traversal) {
+    const uint64_t n = d.hittable_count;
+    if (!d.hittables || !d.world_refs || n == 0 || d.world_count == 0 || d.root_wref >= d.world_count) {
+      out.error = "rt_scene_upload: empty or inconsistent scene description"; return RT_ERR_INVALID;
+    }
+    if (n > INDEX_MASK) { out.error = "rt_scene_upload: too many hittables"; return RT_ERR_UNSUPPORTED; }
+    for (uint64_t i = 0; i < d.world_count; ++i)
+      if (d.world_refs[i] >= n) { out.error = "rt_scene_upload: world ref out of range"; return RT_ERR_INVALID; }
+    // 16-byte aligned copy of the arena (TK_ARENA fallback path)
+    out.tex_arena.assign(d.texture_arena, d.texture_arena + d.texture_bytes);
+    out.tex_arena.resize((out.tex_arena.size() + 31) & ~size_t(15), 0);
+
+    // pass 1: one record per hittable, kinds in their own arrays
+    tag.assign(n, make_ref(K_NONE, 0));
+    uint32_t n_bvh = 0, n_xf = 0, n_st = 0;
+    for (uint64_t i = 0; i < n; ++i) {
+      const rt_hittable &h = H((uint32_t)i);
+      switch (h.type) {
+        case RT_OBJ_SPHERE: tag[i] = make_ref(K_SPHERE, add_sphere(vv(h.u.sphere.center), vv(h.u.sphere.direction), h.u.sphere.radius, h.u.sphere.mat)); break;
+        case RT_OBJ_TRIANGLE: tag[i] = make_ref(K_TRIANGLE, add_planar(h.u.planar.geom, h.u.planar.mat)); break;
+        case RT_OBJ_QUAD: tag[i] = make_ref(K_QUAD, add_planar(h.u.planar.geom, h.u.planar.mat)); break;
+        case RT_OBJ_BVH_NODE: tag[i] = make_ref(K_BVH, n_bvh++); break;
+        case RT_OBJ_TRANSLATION: tag[i] = make_ref(K_TRANSLATION, n_xf++); out.has_wrappers = true; break;
+        case RT_OBJ_Y_ROTATION: tag[i] = make_ref(K_YROTATION, n_xf++); out.has_wrappers = true; break;
+        case RT_OBJ_STRUCTURE: tag[i] = make_ref(K_STRUCTURE, n_st++); break;
+        default: out.error = "rt_scene_upload: unknown hittable type"; return RT_ERR_INVALID;
+      }
+    }
+    // pass 2: links
+    out.ref_nodes.resize(2 * (size_t)n_bvh); out.xforms.resize(n_xf); out.structures.resize(n_st);
+    for (uint64_t i = 0; i < n; ++i) {
+      const rt_hittable &h = H((uint32_t)i);
+      const uint32_t idx = ref_index(tag[i]);
+      if (h.type == RT_OBJ_BVH_NODE) {
+        if (h.u.bvh.left >= d.world_count || h.u.bvh.right >= d.world_count) { out.error = "rt_scene_upload: BVH child out of range"; return RT_ERR_INVALID; }
+        const rt_aabb &b = h.u.bvh.bbox;
+        out.ref_nodes[2 * idx] = f4(b.x0, b.x1, b.y0, b.y1);
+        out.ref_nodes[2 * idx + 1] = f4(b.z0, b.z1, as_float(tag[d.world_refs[h.u.bvh.left]]), as_float(tag[d.world_refs[h.u.bvh.right]]));
+      } else if (h.type == RT_OBJ_TRANSLATION) {
+        if (h.u.translation.child >= n) { out.error = "rt_scene_upload: wrapper child out of range"; return RT_ERR_INVALID; }
+        out.xforms[idx] = f4(h.u.translation.offset.x, h.u.translation.offset.y, h.u.translation.offset.z, as_float(tag[h.u.translation.child]));
+      } else if (h.type == RT_OBJ_Y_ROTATION) {
+        if (h.u.y_rotation.child >= n) { out.error = "rt_scene_upload: wrapper child out of range"; return RT_ERR_INVALID; }
+        out.xforms[idx] = f4(h.u.y_rotation.sin_theta, h.u.y_rotation.cos_theta, 0.0f, as_float(tag[h.u.y_rotation.child]));
+      } else if (h.type == RT_OBJ_STRUCTURE) {
+        if ((uint64_t)h.u.structure.first + h.u.structure.count > n) { out.error = "rt_scene_upload: structure out of range"; return RT_ERR_INVALID; }
+        uint2 s; s.x = (uint32_t)out.struct_children.size(); s.y = (uint32_t)h.u.structure.count;
+        for (uint32_t k = 0; k < s.y; ++k) out.struct_children.push_back(tag[h.u.structure.first + k]);
+        out.structures[idx] = s;
+      }
+    }
+    const uint32_t root_href = d.world_refs[d.root_wref];
+    out.ref_root = tag[root_href];
+    out.ref_stack_need = stack_need(root_href, 0, 0) + 1;
+
+    // own BVH
+    const bool want_fast = traversal == RT_TRAVERSAL_FAST || (traversal == RT_TRAVERSAL_AUTO && !out.has_wrappers);
+    if (want_fast) {
+      Xf id;
+      for (uint64_t w = 0; w < d.world_count; ++w) {
+        const uint32_t href = d.world_refs[w];
+        if (H(href).type != RT_OBJ_BVH_NODE) flatten(href, id, 0);
+      }
+      if (leaves.empty()) { out.error = "rt_scene_upload: no primitives"; return RT_ERR_INVALID; }
+      if (leaves.size() == 1) {                       // a root node with one real child and one empty box
+        out.fast_nodes.resize(4);
+        const Box &b = leaves[0].box;
+        out.fast_nodes[0] = f4(b.lo[0], b.hi[0], b.lo[1], b.hi[1]);
+        out.fast_nodes[1] = f4(INFINITY, -INFINITY, INFINITY, -INFINITY);
+        out.fast_nodes[2] = f4(b.lo[2], b.hi[2], INFINITY, -INFINITY);
+        out.fast_nodes[3] = f4(as_float(leaves[0].ref), as_float(make_ref(K_NONE, 0)), 0.0f, 0.0f);
+        out.fast_root = make_ref(K_BVH, 0);
+        out.fast_stack_need = 2;
+      } else {
+        SahBuilder sb(leaves, out.fast_nodes);
+        Box rb;
+        out.fast_root = sb.build(0, leaves.size(), 0, rb);
+        out.fast_stack_need = sb.max_depth + 2;
+      }
+      out.has_fast = true;
+    }
+    out.traversal_used = want_fast ? RT_TRAVERSAL_FAST : RT_TRAVERSAL_REFERENCE;
+    const uint32_t need = want_fast ? out.fast_stack_need : out.ref_stack_need;
+    if (need > (uint32_t)STACK_CAPACITY) {
+      out.error = "rt_scene_upload: traversal stack need " + std::to_string(need) + " exceeds device capacity " + std::to_string(STACK_CAPACITY);
+      return RT_ERR_UNSUPPORTED;
+    }
+    // materials: prim id = sphere index, or sphere_count + planar index
+    out.sphere_count = (uint32_t)(out.spheres.size() / 2);
+    out.planar_count = (uint32_t)(out.planars.size() / 4);
+    out.materials.resize(2 * (size_t)(out.sphere_count + out.planar_count));
+    for (uint32_t i = 0; i < out.sphere_count; ++i) pack_material(sphere_mats[i], d.texture_arena, d.texture_bytes, out, &out.materials[2 * i]);
+    for (uint32_t i = 0; i < out.planar_count; ++i)
+      pack_material(planar_mats[i], d.texture_arena, d.texture_bytes, out, &out.materials[2 * (size_t)(out.sphere_count + i)]);
+    return RT_OK;
+  }
+};
+
+}  // namespace
+
+int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out) {
+  if (traversal > RT_TRAVERSAL_FAST) { out.error = "rt_scene_upload: unknown traversal mode"; return RT_ERR_INVALID; }
+  Packer p(desc, out);
+  return p.run(traversal);
+}
+
+// ---------------------------------------------------------------------------------------- XORWOW skip-ahead tables
+// One XORWOW step is linear over GF(2) on the 160 state bits v[0..4] (the Weyl counter d is separate and a
+// subsequence jump of 2^67 steps leaves it unchanged mod 2^32).  Row r of a matrix is the image of unit vector e_r.
+void xorwow_sequence_matrices(std::vector<uint32_t> &out) {
+  const int R = 160, W = 5;
+  std::vector<uint32_t> m(R * W), t(R * W);
+  for (int r = 0; r < R; ++r) {
+    uint32_t v[5] = {0, 0, 0, 0, 0};
+    v[r / 32] = 1u << (r & 31);
+    uint32_t x = v[0] ^ (v[0] >> 2);
+    v[0] = v[1]; v[1] = v[2]; v[2] = v[3]; v[3] = v[4];
+    v[4] = (v[4] ^ (v[4] << 4)) ^ (x ^ (x << 1));
+    for (int k = 0; k < W; ++k) m[r * W + k] = v[k];
+  }
+  auto square = [&]() {
+    for (int r = 0; r < R; ++r) {
+      uint32_t acc[5] = {0, 0, 0, 0, 0};
+      for (int i = 0; i < W; ++i)
+        for (int j = 0; j < 32; ++j)
+          if (m[r * W + i] & (1u << j))
+            for (int k = 0; k < W; ++k) acc[k] ^= m[(i * 32 + j) * W + k];
+      for (int k = 0; k < W; ++k) t[r * W + k] = acc[k];
+    }
+    m.swap(t);
+  };
+  for (int i = 0; i < 67; ++i) square();
+  out.resize((size_t)64 * R * W);
+  for (int k = 0; k < 64; ++k) {
+    memcpy(&out[(size_t)k * R * W], m.data(), sizeof(uint32_t) * R * W);
+    square();
+  }
+}
+
+}  // namespace rtp

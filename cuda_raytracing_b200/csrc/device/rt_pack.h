@@ -1,0 +1,42 @@
+// rt_pack.h -- host-side packer: reference-format scene arrays -> device layout (rt_device.h).
+#ifndef RT_PACK_H
+#define RT_PACK_H
+
+#include <stdint.h>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "rt_api.h"
+#include "rt_device.h"
+
+namespace rtp {
+
+struct PackedScene {
+  std::vector<float4> ref_nodes, xforms, fast_nodes, spheres, planars, checkers, perlin_vectors;
+  std::vector<uint2> structures;
+  std::vector<uint32_t> struct_children;
+  std::vector<uint4> materials;          // 2 per primitive id
+  std::vector<uint8_t> perlin_perm, tex_arena;
+  uint32_t ref_root = 0, fast_root = 0;
+  uint32_t sphere_count = 0, planar_count = 0, perlin_tables = 0;
+  bool has_wrappers = false;             // any translation / y-rotation in the scene
+  bool has_fast = false;                 // fast_nodes valid
+  uint32_t ref_stack_need = 0, fast_stack_need = 0;
+  uint32_t traversal_used = 0;           // RT_TRAVERSAL_REFERENCE or RT_TRAVERSAL_FAST
+  std::map<uint64_t, uint32_t> checker_ids, noise_ids;   // arena offset -> table index (dedup)
+  std::string error;
+};
+
+// returns RT_OK or an RT_ERR_* code (text in out.error)
+int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out);
+
+// one reference Material (24 B) -> the two 16-byte words of a device material record, pre-resolving its
+// texture against `arena`; may append to out.checkers / perlin tables.
+void pack_material(const rt_material &m, const uint8_t *arena, uint64_t arena_bytes, PackedScene &out, uint4 rec[2]);
+
+// GF(2) skip-ahead matrices M^(2^(67+k)), k = 0..63, 160 rows x 5 words each (XORWOW subsequence spacing)
+void xorwow_sequence_matrices(std::vector<uint32_t> &out);
+
+}  // namespace rtp
+#endif

@@ -1,0 +1,199 @@
+// rt_shade.cuh -- texture evaluation (solid / checker / image / Perlin noise), emission and material scatter.
+//
+// Replaces texture_get_color, perlin_noise_val/perlin_turbulence, material_emit, material_scatter_common and
+// reflect/refract/reflectance of the reference (rt.cu:343-398, 415-502; perlin_noise.cpp:1-46, 72-85).
+#ifndef RT_SHADE_CUH
+#define RT_SHADE_CUH
+
+#include "rt_device.h"
+#include "rt_math.cuh"
+#include "rt_trace.cuh"
+
+namespace rts {
+using namespace rtm;
+using rtd::Scene;
+
+// Perlin tables of noise texture 0 staged in shared memory (north_star item 3); other tables stay in global.
+struct PerlinSmem {
+  float4 vec[256];
+  uint8_t perm[256];
+};
+
+struct PerlinShared {
+  const PerlinSmem *t;
+  __device__ __forceinline__ V3 vec(int h) const { const float4 c = t->vec[h]; return v3(c.x, c.y, c.z); }
+  __device__ __forceinline__ int perm(int i) const { return t->perm[i & 255]; }
+};
+struct PerlinGlobal {
+  const float4 *v; const uint8_t *p;
+  __device__ __forceinline__ V3 vec(int h) const { const float4 c = __ldg(v + h); return v3(c.x, c.y, c.z); }
+  __device__ __forceinline__ int perm(int i) const { return __ldg(p + (i & 255)); }
+};
+struct PerlinArena {          // reference layout inside the texture arena: vec3[256] then i32 perm_x[256] at +3072
+  const uint8_t *base;
+  __device__ __forceinline__ V3 vec(int h) const {
+    const float *f = reinterpret_cast<const float *>(base) + 3 * h;   // arena copy is 16-byte aligned, offsets are multiples of 4
+    return v3(f[0], f[1], f[2]);
+  }
+  __device__ __forceinline__ int perm(int i) const { return reinterpret_cast<const int *>(base + 3072)[i & 255]; }
+};
+
+// perlin_noise_val + perlin_interp (perlin_noise.cpp:1-46).  perm_x hashes all three axes (lines 37-39).
+template <class T>
+__device__ __forceinline__ float perlin_noise(const T &tab, V3 p) {
+  const float fx = floorf(p.x), fy = floorf(p.y), fz = floorf(p.z);
+  const float u = fsub(p.x, fx), v = fsub(p.y, fy), w = fsub(p.z, fz);
+  const int i = (int)fx, j = (int)fy, k = (int)fz;
+  const float uu = fmul(fmul(u, u), fsub(3.0f, fadd(u, u)));
+  const float vv = fmul(fmul(v, v), fsub(3.0f, fadd(v, v)));
+  const float ww = fmul(fmul(w, w), fsub(3.0f, fadd(w, w)));
+  const float wu[2] = {fsub(1.0f, uu), uu}, wv[2] = {fsub(1.0f, vv), vv}, wwt[2] = {fsub(1.0f, ww), ww};
+  const float du[2] = {u, fadd(u, -1.0f)}, dv[2] = {v, fadd(v, -1.0f)}, dw[2] = {w, fadd(w, -1.0f)};
+  const int pi_[2] = {tab.perm(i), tab.perm(i + 1)};
+  const int pj_[2] = {tab.perm(j), tab.perm(j + 1)};
+  const int pk_[2] = {tab.perm(k), tab.perm(k + 1)};
+  float accum = 0.0f;
+#pragma unroll
+  for (int a = 0; a < 2; ++a)
+#pragma unroll
+    for (int b = 0; b < 2; ++b)
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        const V3 g = tab.vec(pi_[a] ^ pj_[b] ^ pk_[c]);
+        const float d = ffma(dw[c], g.z, ffma(du[a], g.x, fmul(dv[b], g.y)));
+        accum = ffma(fmul(fmul(wu[a], wv[b]), wwt[c]), d, accum);
+      }
+  return accum;
+}
+// perlin_turbulence (perlin_noise.cpp:72-85), depth fixed at 7 by the only call site (rt.cu:393)
+template <class T>
+__device__ __forceinline__ float perlin_turbulence7(const T &tab, V3 p) {
+  float accum = 0.0f, weight = 1.0f;
+#pragma unroll 1
+  for (int o = 0; o < 7; ++o) {
+    accum = ffma(weight, perlin_noise(tab, p), accum);
+    weight = fmul(weight, 0.5f);
+    p = v3(fadd(p.x, p.x), fadd(p.y, p.y), fadd(p.z, p.z));
+  }
+  return fabsf(accum);
+}
+// noise texture colour (rt.cu:386-395): 0.5*(1 + sin(scale*z + 10*turb))
+__device__ __forceinline__ V3 noise_colour(float turb, float scale, float z) {
+  const float c = fmul(fadd(sinf(ffma(z, scale, fmul(turb, 10.0f))), 1.0f), 0.5f);
+  return v3(c, c, c);
+}
+__device__ __forceinline__ bool checker_even(float inv_scale, V3 p) {       // rt.cu:365-371
+  const int x = (int)floorf(fmul(p.x, inv_scale)), y = (int)floorf(fmul(p.y, inv_scale)), z = (int)floorf(fmul(p.z, inv_scale));
+  return ((x + y + z) & 1) == 0;
+}
+
+// texture_get_color over the reference-format arena (generic fallback: nested checkers, image textures,
+// extra noise tables).  The checker recursion of the reference becomes a loop.
+__device__ __noinline__ V3 arena_texture(const Scene &sc, uint32_t off, float u, float v, V3 p) {
+  for (int guard = 0; guard < 64; ++guard) {
+    const uint8_t *t = sc.tex_arena + off;
+    const uint32_t type = *reinterpret_cast<const uint32_t *>(t);
+    if (type == 0) { const float *a = reinterpret_cast<const float *>(t + 8); return v3(a[0], a[1], a[2]); }
+    if (type == 1) {
+      const float inv = *reinterpret_cast<const float *>(t + 8);
+      off = (uint32_t)(checker_even(inv, p) ? *reinterpret_cast<const uint64_t *>(t + 16) : *reinterpret_cast<const uint64_t *>(t + 24));
+      continue;
+    }
+    if (type == 2) {                                                          // rt.cu:377-385, 343-354
+      const int width = *reinterpret_cast<const int *>(t + 24), height = *reinterpret_cast<const int *>(t + 28);
+      const float uc = u < 0.0f ? 0.0f : (u > 1.0f ? 1.0f : u);
+      const float vc = fsub(1.0f, v < 0.0f ? 0.0f : (v > 1.0f ? 1.0f : v));
+      int x = (int)fmul(uc, (float)width), y = (int)fmul(vc, (float)height);
+      if (*reinterpret_cast<const uint64_t *>(t + 8) == 0) return v3(1.0f, 0.0f, 1.0f);   // pixels == NULL
+      x = x < 0 ? 0 : (x > width ? width : x);
+      y = y < 0 ? 0 : (y > height ? height : y);
+      const float *px = reinterpret_cast<const float *>(sc.tex_arena + *reinterpret_cast<const uint64_t *>(t + 16)) + 3 * (y * width + x);
+      return v3(px[0], px[1], px[2]);
+    }
+    if (type == 3) {
+      PerlinArena tab; tab.base = sc.tex_arena + *reinterpret_cast<const uint64_t *>(t + 16);
+      return noise_colour(perlin_turbulence7(tab, p), *reinterpret_cast<const float *>(t + 24), p.z);
+    }
+    break;
+  }
+  return v3(0.0f, 0.0f, 0.0f);
+}
+
+// colour of the texture a lambertian / light material refers to
+__device__ __forceinline__ V3 material_texture(const Scene &sc, const uint4 m0, const float4 m1, const rtt::Hit &h,
+                                               const PerlinSmem *smem_perlin) {
+  const uint32_t kind = (m0.x >> 8) & 0xffu;
+  if (kind == rtd::TK_SOLID) return v3(m1.x, m1.y, m1.z);
+  if (kind == rtd::TK_CHECKER_SOLID) {
+    const float4 c0 = __ldg(sc.checkers + 2 * m0.z);
+    if (checker_even(c0.x, h.p)) return v3(c0.y, c0.z, c0.w);
+    const float4 c1 = __ldg(sc.checkers + 2 * m0.z + 1);
+    return v3(c1.y, c1.z, c1.w);
+  }
+  if (kind == rtd::TK_NOISE) {
+    float turb;
+    if (m0.z == 0 && smem_perlin) { PerlinShared tab; tab.t = smem_perlin; turb = perlin_turbulence7(tab, h.p); }
+    else { PerlinGlobal tab; tab.v = sc.perlin_vectors + 256 * m0.z; tab.p = sc.perlin_perm + 256 * m0.z; turb = perlin_turbulence7(tab, h.p); }
+    return noise_colour(turb, m1.w, h.p.z);
+  }
+  return arena_texture(sc, m0.y, h.u, h.v, h.p);
+}
+
+__device__ __forceinline__ V3 unit_or_zero(V3 a, float len) {                 // vec3_to_unit_vec (vec3.h:105-114)
+  if (len == 0.0f) return v3(0.0f, 0.0f, 0.0f);
+  return v3(fdiv(a.x, len), fdiv(a.y, len), fdiv(a.z, len));
+}
+
+// material_scatter_common (rt.cu:452-490).  `U` and `rtest` are drawn by the caller for EVERY hit, whatever the
+// material (rt.cu:500-501, Q5).  Returns false when the path ends here (absorbed metal bounce, or a light).
+__device__ __forceinline__ bool scatter(const Scene &sc, const uint4 m0, const float4 m1, const V3 din, const rtt::Hit &h,
+                                        const V3 U, const float rtest, const PerlinSmem *smem_perlin, V3 &dout, V3 &att) {
+  const V3 n = h.n;
+  const uint32_t type = m0.x & 0xffu;
+  if (type == rtd::M_LAMBERTIAN) {
+    V3 d = vadd(n, U);
+    const float tiny = 1e-8f;                                                 // vec3_is_near_zero (vec3.h:177-181)
+    if (fabsf(d.x) < tiny && fabsf(d.y) < tiny && fabsf(d.z) < tiny) d = n;
+    dout = d;
+    att = material_texture(sc, m0, m1, h, smem_perlin);
+    return true;
+  }
+  if (type == rtd::M_METAL) {
+    const float dn = dot_xfirst(n, din);                                      // reflect (rt.cu:424-429)
+    const float two = fadd(dn, dn);
+    const V3 r = v3(ffma(-n.x, two, din.x), ffma(-n.y, two, din.y), ffma(-n.z, two, din.z));
+    const V3 ru = unit_or_zero(r, fsqrt(dot_yfirst(r, r)));
+    dout = v3(ffma(m1.w, U.x, ru.x), ffma(m1.w, U.y, ru.y), ffma(m1.w, U.z, ru.z));
+    att = v3(m1.x, m1.y, m1.z);
+    return dot_yfirst(n, dout) > 0.0f;
+  }
+  if (type == rtd::M_DIELECTRIC) {
+    att = v3(1.0f, 1.0f, 1.0f);
+    const float ri = h.front ? frcp(m1.w) : m1.w;
+    const V3 u = unit_or_zero(din, fsqrt(dot_xfirst(din, din)));
+    const float nxux = fmul(n.x, u.x), nzuz = fmul(n.z, u.z);
+    const float cos_theta = fminf(fsub(ffma(n.y, -u.y, -nxux), nzuz), 1.0f);  // fmin(dot(-u, n), 1)
+    const float sin_theta = fsqrt(ffma(-cos_theta, cos_theta, 1.0f));
+    bool reflect_it = fmul(ri, sin_theta) > 1.0f;
+    if (!reflect_it) {                                                        // Schlick reflectance (rt.cu:431-437)
+      const float r0 = fdiv(fsub(1.0f, ri), fadd(ri, 1.0f));
+      const float r0sq = fmul(r0, r0);
+      reflect_it = ffma(fsub(1.0f, r0sq), powf(fsub(1.0f, cos_theta), 5.0f), r0sq) > rtest;
+    }
+    if (reflect_it) {
+      const float dn = fadd(nzuz, ffma(n.y, u.y, nxux));
+      const float two = fadd(dn, dn);
+      dout = v3(ffma(-n.x, two, u.x), ffma(-n.y, two, u.y), ffma(-n.z, two, u.z));
+    } else {                                                                  // refract (rt.cu:415-422)
+      const V3 perp = v3(fmul(ffma(n.x, cos_theta, u.x), ri), fmul(ffma(n.y, cos_theta, u.y), ri), fmul(ffma(n.z, cos_theta, u.z), ri));
+      const float plen = fsqrt(dot_yfirst(perp, perp));
+      const float k = fsqrt(fabsf(ffma(-plen, plen, 1.0f)));
+      dout = v3(ffma(-n.x, k, perp.x), ffma(-n.y, k, perp.y), ffma(-n.z, k, perp.z));
+    }
+    return true;
+  }
+  return false;                                                               // DIFFUSE_LIGHT: no scatter
+}
+
+}  // namespace rts
+#endif

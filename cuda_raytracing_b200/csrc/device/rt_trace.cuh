@@ -1,0 +1,236 @@
+// rt_trace.cuh -- ray/primitive intersection and the two closest-hit traversals.
+//
+// Replaces hit() / aabb_hit() / geom_calc_hit() of the reference (rt.cu:989-1025, 1060-1077, 1079-1251).
+// Arithmetic that decides or produces a hit follows the reference kernel's roundings (rt_math.cuh).
+#ifndef RT_TRACE_CUH
+#define RT_TRACE_CUH
+
+#include "rt_device.h"
+#include "rt_math.cuh"
+
+namespace rtt {
+using namespace rtm;
+using rtd::Scene;
+
+struct Ray { V3 o, d; float time; };
+
+struct Hit {
+  V3 p, n;          // point, normal (already flipped against the ray)
+  float t, u, v;
+  uint32_t prim;    // primitive id: sphere index, or sphere_count + planar index
+  int front;
+};
+
+__device__ __forceinline__ float4 ldg4(const float4 *p) { return __ldg(p); }
+
+// ---- sphere (rt.cu:1093-1123): a = d.d is passed in (it only changes when a wrapper rotates the ray) ----
+__device__ __forceinline__ bool hit_sphere(const Scene &sc, uint32_t idx, const Ray &r, float a, float tmin, float &tmax,
+                                           Hit &h) {
+  const float4 s0 = ldg4(sc.spheres + 2 * idx);
+  const float4 s1 = ldg4(sc.spheres + 2 * idx + 1);
+  const V3 c = v3(ffma(r.time, s1.x, s0.x), ffma(r.time, s1.y, s0.y), ffma(r.time, s1.z, s0.z));   // movement_path_at
+  const V3 oc = vsub(c, r.o);
+  const float b = fmul(dot_yfirst(r.d, oc), -2.0f);
+  const float cc = ffma(-s0.w, s0.w, dot_yfirst(oc, oc));
+  const float disc = ffma(b, b, fmul(cc, fmul(a, -4.0f)));
+  if (!(disc >= 0.0f)) return false;
+  const float sq = fsqrt(disc);
+  const float a2 = fadd(a, a);
+  float root = fdiv(fsub(-b, sq), a2);
+  if (tmin >= root || root >= tmax) root = fdiv(fsub(sq, b), a2);
+  if (!(tmin < root && root < tmax)) return false;
+  h.t = root;
+  h.p = along(r.o, root, r.d);
+  const float inv_r = frcp(s0.w);
+  const V3 pc = vsub(h.p, c);
+  const V3 n = v3(fmul(pc.x, inv_r), fmul(pc.y, inv_r), fmul(pc.z, inv_r));
+  if (__float_as_uint(s1.w) & 1u) {                       // sphere_get_uv (rt.cu:583-590): only image textures read it
+    const float pi = 3.1415926535897932385f;
+    const float theta = acosf(-n.y);
+    const float phi = fadd(atan2f(-n.z, n.x), pi);
+    h.u = fdiv(phi, fmul(2.0f, pi));
+    h.v = fdiv(theta, pi);
+  }
+  h.front = dot_yfirst(r.d, n) < 0.0f;                     // hit_record_set_face_normal (rt.cu:983-987)
+  h.n = h.front ? n : vneg(n);
+  h.prim = idx;
+  tmax = root;
+  return true;
+}
+
+// ---- quad / triangle (rt.cu:1131-1175 with geom_calc_hit 1060-1077) ----
+__device__ __forceinline__ bool hit_planar(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float tmin, float &tmax,
+                                           Hit &h) {
+  const float4 p0 = ldg4(sc.planars + 4 * idx);            // normal, d
+  const V3 n = v3(p0.x, p0.y, p0.z);
+  const float denom = dot_yfirst(n, r.d);
+  // reference: fabsf(denom) >= 1e-8 evaluated in double; (float)1e-8 < 1e-8, so in f32 this is a strict '>'
+  if (!(fabsf(denom) > 1e-8f)) return false;
+  const float t = fdiv(fsub(p0.w, dot_yfirst(n, r.o)), denom);
+  if (!(tmin <= t && t <= tmax)) return false;
+  const float4 p1 = ldg4(sc.planars + 4 * idx + 1);        // q, w.x
+  const float4 p2 = ldg4(sc.planars + 4 * idx + 2);        // v, w.y
+  const float4 p3 = ldg4(sc.planars + 4 * idx + 3);        // u, w.z
+  const V3 p = along(r.o, t, r.d);
+  const V3 pl = vsub(p, v3(p1.x, p1.y, p1.z));
+  const V3 w = v3(p1.w, p2.w, p3.w);
+  const float alpha = dot_yfirst(w, cross(pl, v3(p2.x, p2.y, p2.z)));
+  const float beta = dot_yfirst(w, cross(v3(p3.x, p3.y, p3.z), pl));
+  bool inside = (0.0f <= alpha && alpha <= 1.0f) && (0.0f <= beta && beta <= 1.0f);
+  if (triangle) inside = inside && (fadd(alpha, beta) <= 1.0f);
+  if (!inside) return false;
+  h.u = alpha; h.v = beta; h.t = t; h.p = p;
+  h.front = denom < 0.0f;
+  h.n = h.front ? n : vneg(n);
+  h.prim = sc.sphere_count + idx;
+  tmax = t;
+  return true;
+}
+
+// ---- aabb_hit exactly as the reference (rt.cu:989-1025): (a<b) selects, per-axis early-out, NaNs flow through ----
+__device__ __forceinline__ bool aabb_axis(float lo, float hi, float o, float inv, float &t0, float &t1) {
+  float ta = fmul(fsub(lo, o), inv);
+  float tb = fmul(fsub(hi, o), inv);
+  if (inv < 0.0f && ta > tb) { float s = ta; ta = tb; tb = s; }
+  t0 = (t0 < ta) ? ta : t0;
+  t1 = (t1 < tb) ? t1 : tb;
+  return !(t1 <= t0);
+}
+
+// ================= reference-order traversal (instance wrappers, reference BVH, reference visiting order) ======
+// Returns true when something was hit.  The ray is edited in place by the wrappers and, like the reference,
+// comes back with the rounding drift of the un-rotate / un-translate (Q12).
+template <int STRIDE_IS_BLOCKDIM = 1>
+__device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float tmin, float tmax, Hit &h,
+                                                uint32_t *stk, const int stride) {
+  bool result = false, was_last_hit = false, in_translation = false, in_rotation = false;
+  int sp = 0;
+  stk[0] = sc.ref_root; sp = 1;
+  V3 inv = v3(frcp(r.d.x), frcp(r.d.y), frcp(r.d.z));
+  float a = dot_xfirst(r.d, r.d);
+  while (sp > 0) {
+    const uint32_t cur = stk[(--sp) * stride];
+    const uint32_t idx = rtd::ref_index(cur);
+    switch (rtd::ref_kind(cur)) {
+      case rtd::K_SPHERE:
+        if (hit_sphere(sc, idx, r, a, tmin, tmax, h)) { result = true; if (in_translation || in_rotation) was_last_hit = true; }
+        break;
+      case rtd::K_TRIANGLE:
+      case rtd::K_QUAD:
+        if (hit_planar(sc, idx, rtd::ref_kind(cur) == rtd::K_TRIANGLE, r, tmin, tmax, h)) {
+          result = true; if (in_translation || in_rotation) was_last_hit = true;
+        }
+        break;
+      case rtd::K_BVH: {
+        const float4 n0 = ldg4(sc.ref_nodes + 2 * idx);
+        const float4 n1 = ldg4(sc.ref_nodes + 2 * idx + 1);
+        float t0 = tmin, t1 = tmax;
+        if (aabb_axis(n0.x, n0.y, r.o.x, inv.x, t0, t1) && aabb_axis(n0.z, n0.w, r.o.y, inv.y, t0, t1) &&
+            aabb_axis(n1.x, n1.y, r.o.z, inv.z, t0, t1)) {
+          stk[(sp++) * stride] = __float_as_uint(n1.w);    // right first => left is visited first (Q11)
+          stk[(sp++) * stride] = __float_as_uint(n1.z);
+        }
+      } break;
+      case rtd::K_TRANSLATION: {
+        const float4 x = ldg4(sc.xforms + idx);
+        const V3 off = v3(x.x, x.y, x.z);
+        if (!in_translation) {
+          was_last_hit = false;
+          r.o = vsub(r.o, off);
+          stk[(sp++) * stride] = cur;
+          stk[(sp++) * stride] = __float_as_uint(x.w);
+          in_translation = true;
+        } else {
+          r.o = vadd(r.o, off);
+          in_translation = false;
+          if (was_last_hit) h.p = vadd(h.p, off);
+        }
+      } break;
+      case rtd::K_YROTATION: {
+        const float4 x = ldg4(sc.xforms + idx);
+        const float sn = x.x, cs = x.y;
+        if (!in_rotation) {                                 // rt.cu:1194-1209, roundings from the reference's SASS
+          was_last_hit = false;
+          const V3 o = r.o, d = r.d;
+          r.o = v3(ffma(o.x, cs, -fmul(o.z, sn)), o.y, ffma(o.x, sn, fmul(o.z, cs)));
+          r.d = v3(ffma(d.x, cs, -fmul(d.z, sn)), d.y, ffma(d.z, cs, fmul(d.x, sn)));
+          stk[(sp++) * stride] = cur;
+          stk[(sp++) * stride] = __float_as_uint(x.w);
+          in_rotation = true;
+        } else {                                            // rt.cu:1210-1236
+          const V3 o = r.o, d = r.d;
+          r.o = v3(ffma(o.x, cs, fmul(o.z, sn)), o.y, ffma(o.z, cs, -fmul(o.x, sn)));
+          r.d = v3(ffma(d.x, cs, fmul(d.z, sn)), d.y, ffma(d.z, cs, -fmul(d.x, sn)));
+          in_rotation = false;
+          if (was_last_hit) {
+            const V3 p = h.p, n = h.n;
+            h.p = v3(ffma(p.x, cs, fmul(p.z, sn)), p.y, ffma(p.z, cs, -fmul(p.x, sn)));
+            h.n = v3(ffma(n.x, cs, fmul(n.z, sn)), n.y, ffma(n.z, cs, -fmul(n.x, sn)));
+          }
+        }
+        inv.x = frcp(r.d.x); inv.z = frcp(r.d.z);
+        a = dot_xfirst(r.d, r.d);
+      } break;
+      case rtd::K_STRUCTURE: {
+        const uint2 s = __ldg(sc.structures + idx);
+        for (uint32_t i = 0; i < s.y; ++i) stk[(sp++) * stride] = __ldg(sc.struct_children + s.x + i);
+      } break;
+      default: break;
+    }
+  }
+  return result;
+}
+
+// ================= own BVH (SAH, world-space primitives, near child first) =====================================
+// Closest hit is independent of visiting order and of (conservative) box culling, so for scenes without
+// instance wrappers this returns bit-identical hits to trace_reference at a fraction of the node visits.
+__device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float tmin, float tmax, Hit &h,
+                                           uint32_t *stk, const int stride) {
+  bool result = false;
+  const V3 inv = v3(frcp(r.d.x), frcp(r.d.y), frcp(r.d.z));
+  const float a = dot_xfirst(r.d, r.d);
+  int sp = 0;
+  uint32_t cur = sc.fast_root;
+  for (;;) {
+    const uint32_t kind = rtd::ref_kind(cur);
+    const uint32_t idx = rtd::ref_index(cur);
+    if (kind == rtd::K_BVH) {
+      const float4 n0 = ldg4(sc.fast_nodes + 4 * idx);
+      const float4 n1 = ldg4(sc.fast_nodes + 4 * idx + 1);
+      const float4 n2 = ldg4(sc.fast_nodes + 4 * idx + 2);
+      const float4 n3 = ldg4(sc.fast_nodes + 4 * idx + 3);
+      // slab test of both children; fminf/fmaxf drop NaNs (0*inf) which keeps the test conservative
+      const float c0x0 = (n0.x - r.o.x) * inv.x, c0x1 = (n0.y - r.o.x) * inv.x;
+      const float c0y0 = (n0.z - r.o.y) * inv.y, c0y1 = (n0.w - r.o.y) * inv.y;
+      const float c0z0 = (n2.x - r.o.z) * inv.z, c0z1 = (n2.y - r.o.z) * inv.z;
+      const float c1x0 = (n1.x - r.o.x) * inv.x, c1x1 = (n1.y - r.o.x) * inv.x;
+      const float c1y0 = (n1.z - r.o.y) * inv.y, c1y1 = (n1.w - r.o.y) * inv.y;
+      const float c1z0 = (n2.z - r.o.z) * inv.z, c1z1 = (n2.w - r.o.z) * inv.z;
+      const float e0 = fmaxf(fmaxf(fminf(c0x0, c0x1), fminf(c0y0, c0y1)), fmaxf(fminf(c0z0, c0z1), tmin));
+      const float x0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), tmax));
+      const float e1 = fmaxf(fmaxf(fminf(c1x0, c1x1), fminf(c1y0, c1y1)), fmaxf(fminf(c1z0, c1z1), tmin));
+      const float x1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), tmax));
+      const bool h0 = e0 <= x0, h1 = e1 <= x1;
+      const uint32_t r0 = __float_as_uint(n3.x), r1 = __float_as_uint(n3.y);
+      if (h0 && h1) {
+        const bool swap = e1 < e0;
+        cur = swap ? r1 : r0;
+        stk[(sp++) * stride] = swap ? r0 : r1;
+        continue;
+      } else if (h0 || h1) {
+        cur = h0 ? r0 : r1;
+        continue;
+      }
+    } else if (kind == rtd::K_SPHERE) {
+      result |= hit_sphere(sc, idx, r, a, tmin, tmax, h);
+    } else {
+      result |= hit_planar(sc, idx, kind == rtd::K_TRIANGLE, r, tmin, tmax, h);
+    }
+    if (sp == 0) break;
+    cur = stk[(--sp) * stride];
+  }
+  return result;
+}
+
+}  // namespace rtt
+#endif

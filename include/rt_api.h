@@ -1,0 +1,125 @@
+/* rt_api.h -- the C ABI of libraytracing_b200.so: the drop-in boundary of the path-tracing hot path.
+ *
+ * The reference (luk-zm/cuda_raytracing) has no plugin/FFI layer; its de-facto boundary is
+ *     void render(World *world, RenderSettings *settings)            src/raytracing.cu:1649-1773
+ * which uploads three flat arrays, launches init_gpu_data + cuda_calc and downloads the image.
+ * Each entry point below names the part of render() it replaces.  Plain pointers and sizes only:
+ * no CUDA, C++ or torch types cross this boundary.  Every function returns 0 (RT_OK) or a negative
+ * RT_ERR_* code; rt_last_error_string() gives the text.  One context = one GPU = one host thread at a
+ * time (distinct contexts are independent), like the reference's single synchronous default stream.
+ *
+ * There is NO CPU fallback: without a CUDA device rt_context_create() fails with RT_ERR_CUDA.
+ */
+#ifndef RT_API_H
+#define RT_API_H
+
+#include <stdint.h>
+#include "rt_scene.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+  RT_OK = 0,
+  RT_ERR_INVALID = -1,      /* bad argument */
+  RT_ERR_CUDA = -2,         /* CUDA runtime error (text in rt_last_error_string) */
+  RT_ERR_NO_SCENE = -3,     /* rt_render* before rt_scene_upload */
+  RT_ERR_UNSUPPORTED = -4,  /* scene exceeds a device limit (stack depth, u16 refs, ...) */
+  RT_ERR_NOMEM = -5,
+  RT_ERR_IO = -6
+};
+
+typedef struct rt_context rt_context;
+
+/* replaces: implicit device 0 / default stream of the reference (rt.cu:1694-1748 never selects one) */
+int  rt_context_create(int device_id, rt_context **out);
+void rt_context_destroy(rt_context *ctx);                 /* frees every device allocation (the reference never does) */
+const char *rt_last_error_string(const rt_context *ctx);  /* ctx may be NULL: last global error */
+/* use the caller's CUDA stream (cudaStream_t passed as void*; NULL = the context's own stream) */
+int  rt_context_set_stream(rt_context *ctx, void *cuda_stream);
+
+/* ---- scene upload: replaces the 4 cudaMalloc+cudaMemcpy blocks of render() (rt.cu:1699-1733) ----
+ * Input is the reference's own scene format AFTER make_bvh(): Hittable[120 B], u16 world refs (prims
+ * then BVH nodes), root world ref, texture byte arena.  The callee copies and repacks (SoA primitives,
+ * 128-bit packed nodes); the caller keeps ownership of its arrays. */
+typedef struct rt_scene_desc {
+  const rt_hittable *hittables;  uint64_t hittable_count;
+  const uint16_t *world_refs;    uint64_t world_count;
+  uint32_t root_wref;
+  const uint8_t *texture_arena;  uint64_t texture_bytes;
+} rt_scene_desc;
+
+enum {
+  RT_TRAVERSAL_AUTO = 0,       /* EXACT results: own SAH BVH when the scene has no instance wrappers (closest hit is
+                                  order-independent), the reference's BVH and visiting order otherwise */
+  RT_TRAVERSAL_REFERENCE = 1,  /* always walk the reference's own BVH in the reference's order */
+  RT_TRAVERSAL_FAST = 2        /* instances flattened to world space + SAH BVH: statistical (tier-2) parity only
+                                  when the scene has wrappers, identical to AUTO otherwise */
+};
+int rt_scene_upload(rt_context *ctx, const rt_scene_desc *scene, uint32_t traversal);
+
+/* ---- render: replaces init_gpu_data<<<>>> + cuda_calc<<<>>> (rt.cu:1739-1761) and the D2H (1770-1771) ----
+ * The vectors are exactly the by-value arguments of cuda_calc (rt.cu:1544-1547); rt_camera_setup()
+ * (rt_scene.h) derives them from an rt_render_settings the way render() does (rt.cu:1657-1692). */
+enum {
+  RT_RENDER_OUTPUT_SUM = 1u,      /* leave the per-pixel SUM over samples (for multi-GPU sample sharding + reduce) */
+  RT_RENDER_NO_RNG_CACHE = 2u,    /* recompute the XORWOW states even if cached from the previous call */
+  RT_RENDER_COUNT_RAYS = 4u       /* fill rt_stats.rays (warp-aggregated counter; small cost) */
+};
+typedef struct rt_render_params {
+  int32_t img_width, img_height;
+  int32_t samples_per_pixel, max_bounces;
+  float defocus_angle;
+  float background[3];
+  float pixel_delta_v[3], pixel_delta_u[3], camera_pos[3], defocus_disk_u[3], defocus_disk_v[3], pixel00[3];
+  uint64_t seed;                  /* 1234 in the reference (rt.cu:1747) */
+  uint64_t subsequence_offset;    /* XORWOW subsequence = pixel index + this; 0 = the reference's stream */
+  int32_t row_begin, row_end;     /* render rows [row_begin,row_end) only (tile sharding); 0,0 = whole image */
+  uint32_t flags;
+  uint32_t reserved;
+} rt_render_params;
+
+typedef struct rt_stats {
+  double rng_init_ms, render_ms, resolve_ms;   /* CUDA-event times on the context's stream */
+  double h2d_ms, d2h_ms, total_ms;             /* host wall clock (rt_render only) */
+  uint64_t paths, rays;
+  uint32_t kernel_launches;
+  uint32_t traversal_used;                     /* RT_TRAVERSAL_REFERENCE or RT_TRAVERSAL_FAST */
+  uint32_t grid_blocks, block_threads, regs_per_thread, blocks_per_sm;
+} rt_stats;
+
+void rt_render_params_from_camera(const rt_render_settings *s, const rt_camera *c, rt_render_params *p);
+
+/* device-resident: d_pixels_rgb is a DEVICE pointer to img_width*img_height*3 floats (caller-owned, e.g. a torch
+ * tensor); rows outside [row_begin,row_end) are left untouched.  Asynchronous on the context's stream except
+ * for stats (stats != NULL synchronises). */
+int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels_rgb, rt_stats *stats);
+/* gamma + clamp + 8-bit quantise on the device (rt.cu:1391-1433): rgb8 = (u8)(256*clamp(sqrt(scale*x),0,0.999)) */
+int rt_resolve_device(rt_context *ctx, const float *d_pixels_rgb, uint64_t n_pixels, float scale, uint8_t *d_rgb8);
+/* host buffers: renders, resolves and copies back (h_rgb8 and/or h_pixels_rgb may be NULL) */
+int rt_render(rt_context *ctx, const rt_render_params *p, float *h_pixels_rgb, uint8_t *h_rgb8, rt_stats *stats);
+int rt_synchronize(rt_context *ctx);
+
+/* ---- the whole of render(World*, RenderSettings*) in one call (BVH build if needed, camera, upload, render) ---- */
+int rt_render_world(rt_context *ctx, rt_world *world, const rt_render_settings *settings, uint32_t traversal,
+                    float *h_pixels_rgb, uint8_t *h_rgb8, rt_stats *stats);
+
+/* ---- per-function probes used by the parity tests (same kernels' device functions, batch in / batch out) ---- */
+typedef struct rt_probe_hit {          /* one per ray; mirrors the reference's HitRecord fields + the mutated ray */
+  float origin[3], direction[3];       /* ray AFTER traversal (instance wrappers edit it in place, Q12) */
+  float point[3], normal[3];
+  float t, u, v;
+  int32_t hit, front, material_type;
+} rt_probe_hit;
+int rt_probe_trace(rt_context *ctx, uint64_t n, const float *origins, const float *directions, const float *times,
+                   float tmin, float tmax, rt_probe_hit *out);
+int rt_probe_scatter(rt_context *ctx, uint64_t n, const uint32_t *material6, const float *dir_in, const rt_probe_hit *rec,
+                     const float *unit_vec, const float *random_test, float *dir_out, float *atten_out, int32_t *scattered);
+int rt_probe_texture(rt_context *ctx, uint64_t n, uint64_t texture_offset, const float *uv, const float *points, float *rgb_out);
+int rt_probe_xorwow(rt_context *ctx, uint64_t seed, uint64_t first_subsequence, uint64_t n, uint32_t *states6_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_API_H */
