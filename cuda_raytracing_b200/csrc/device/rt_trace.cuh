@@ -223,9 +223,9 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
       }
     } else if (kind == rtd::K_SPHERE) {
       result |= hit_sphere(sc, idx, r, a, tmin, tmax, h);
-    } else {
+    } else if (kind == rtd::K_QUAD || kind == rtd::K_TRIANGLE) {
       result |= hit_planar(sc, idx, kind == rtd::K_TRIANGLE, r, tmin, tmax, h);
-    }
+    }                                                     // K_NONE: the empty second child of a one-primitive scene
     if (sp == 0) break;
     cur = stk[(--sp) * stride];
   }
