@@ -12,7 +12,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libraytracing_b200.so")
 
 RT_TRAVERSAL_AUTO, RT_TRAVERSAL_REFERENCE, RT_TRAVERSAL_FAST = 0, 1, 2
-RT_RENDER_OUTPUT_SUM, RT_RENDER_NO_RNG_CACHE, RT_RENDER_COUNT_RAYS = 1, 2, 4
+RT_RENDER_OUTPUT_SUM, RT_RENDER_NO_RNG_CACHE, RT_RENDER_COUNT_RAYS, RT_RENDER_COUNT_OPS = 1, 2, 4, 8
+OP_NAMES = ["box", "sphere", "planar", "translation", "rotation", "lambert", "metal", "glass", "light", "noise", "checker", "arena"]
 
 
 class RtError(RuntimeError):
@@ -63,7 +64,7 @@ class Stats(C.Structure):  # rt_stats
                 ("h2d_ms", C.c_double), ("d2h_ms", C.c_double), ("total_ms", C.c_double),
                 ("paths", C.c_uint64), ("rays", C.c_uint64), ("kernel_launches", C.c_uint32),
                 ("traversal_used", C.c_uint32), ("grid_blocks", C.c_uint32), ("block_threads", C.c_uint32),
-                ("regs_per_thread", C.c_uint32), ("blocks_per_sm", C.c_uint32)]
+                ("regs_per_thread", C.c_uint32), ("blocks_per_sm", C.c_uint32), ("ops", C.c_uint64 * 12)]
 
 
 class ProbeHit(C.Structure):  # rt_probe_hit
@@ -74,7 +75,7 @@ class ProbeHit(C.Structure):  # rt_probe_hit
 
 EXPORTS = [
     # rt_api.h
-    "rt_context_create", "rt_context_destroy", "rt_last_error_string", "rt_context_set_stream", "rt_scene_upload",
+    "rt_context_create", "rt_context_destroy", "rt_last_error_string", "rt_context_set_stream", "rt_context_reset_stream", "rt_scene_upload",
     "rt_render_params_from_camera", "rt_render_device", "rt_resolve_device", "rt_render", "rt_synchronize",
     "rt_render_world", "rt_probe_trace", "rt_probe_scatter", "rt_probe_texture", "rt_probe_xorwow",
     # rt_scene.h
@@ -102,6 +103,7 @@ def lib():
         L.rt_context_destroy.argtypes = [C.c_void_p]
         L.rt_context_destroy.restype = None
         L.rt_context_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        L.rt_context_reset_stream.argtypes = [C.c_void_p]
         L.rt_scene_upload.argtypes = [C.c_void_p, C.POINTER(SceneDesc), C.c_uint32]
         L.rt_render_params_from_camera.argtypes = [C.POINTER(RenderSettings), C.POINTER(Camera), C.POINTER(RenderParams)]
         L.rt_render_params_from_camera.restype = None
@@ -226,7 +228,11 @@ class Context:
             pass
 
     def set_stream(self, stream_ptr):
-        _check(lib().rt_context_set_stream(self._h, C.c_void_p(stream_ptr)), self._h)
+        """Enqueue on this cudaStream_t (0 = the CUDA default stream); None = back to the context's own stream."""
+        if stream_ptr is None:
+            _check(lib().rt_context_reset_stream(self._h), self._h)
+        else:
+            _check(lib().rt_context_set_stream(self._h, C.c_void_p(stream_ptr)), self._h)
 
     def upload(self, scene, traversal=RT_TRAVERSAL_AUTO):
         d = scene.desc() if isinstance(scene, HostScene) else scene

@@ -101,7 +101,7 @@ int rt_context_create(int device_id, rt_context **out) {
   std::vector<uint32_t> mats;
   rtp::xorwow_sequence_matrices(mats);
   e = ctx->b_rng_mats.upload(mats.data(), mats.size() * sizeof(uint32_t), ctx->stream);
-  if (e == cudaSuccess) e = ctx->b_counters.reserve(2 * sizeof(unsigned long long));
+  if (e == cudaSuccess) e = ctx->b_counters.reserve(16 * sizeof(unsigned long long));
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
   if (e != cudaSuccess) { rt_context_destroy(ctx); return cuda_fail(nullptr, e, "rt_context_create upload"); }
   *out = ctx;
@@ -124,7 +124,13 @@ void rt_context_destroy(rt_context *ctx) {
 
 int rt_context_set_stream(rt_context *ctx, void *cuda_stream) {
   if (!ctx) return fail(nullptr, RT_ERR_INVALID, "rt_context_set_stream: ctx is NULL");
-  ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+  ctx->stream = (cudaStream_t)cuda_stream;
+  return RT_OK;
+}
+
+int rt_context_reset_stream(rt_context *ctx) {
+  if (!ctx) return fail(nullptr, RT_ERR_INVALID, "rt_context_reset_stream: ctx is NULL");
+  ctx->stream = ctx->own_stream;
   return RT_OK;
 }
 
@@ -199,7 +205,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
     ++launches;
   }
   if (stats) RT_CUDA(ctx, cudaEventRecord(ctx->ev[1], s));
-  RT_CUDA(ctx, cudaMemsetAsync(ctx->b_counters.ptr, 0, 2 * sizeof(unsigned long long), s));
+  RT_CUDA(ctx, cudaMemsetAsync(ctx->b_counters.ptr, 0, 16 * sizeof(unsigned long long), s));
 
   rtd::RenderArgs a;
   memset(&a, 0, sizeof(a));
@@ -215,13 +221,14 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   memcpy(a.cam, p->camera_pos, 12); memcpy(a.ddu, p->defocus_disk_u, 12); memcpy(a.ddv, p->defocus_disk_v, 12);
   memcpy(a.p00, p->pixel00, 12);
   a.sample_scale = (p->flags & RT_RENDER_OUTPUT_SUM) ? 1.0f : 1.0f / (float)p->samples_per_pixel;   // rt.cu:1657
-  a.count_rays = (p->flags & RT_RENDER_COUNT_RAYS) ? 1u : 0u;
+  a.count_rays = (p->flags & (RT_RENDER_COUNT_RAYS | RT_RENDER_COUNT_OPS)) ? 1u : 0u;
+  a.count_ops = (p->flags & RT_RENDER_COUNT_OPS) ? 1u : 0u;
   const int mode = ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? 1 : 0;
   RT_CUDA(ctx, rtk::launch_render(a, mode, ctx->sm_count, s, &ctx->last_launch));
   ++launches;
   if (stats) {
     RT_CUDA(ctx, cudaEventRecord(ctx->ev[2], s));
-    unsigned long long counters[2] = {0, 0};
+    unsigned long long counters[16] = {0};
     RT_CUDA(ctx, cudaMemcpyAsync(counters, ctx->b_counters.ptr, sizeof(counters), cudaMemcpyDeviceToHost, s));
     RT_CUDA(ctx, cudaStreamSynchronize(s));
     float t_rng = 0, t_render = 0;
@@ -231,6 +238,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
     stats->rng_init_ms = t_rng; stats->render_ms = t_render;
     stats->paths = count * (uint64_t)(p->samples_per_pixel > 0 ? p->samples_per_pixel : 0);
     stats->rays = counters[1];
+    for (int k = 0; k < 12; ++k) stats->ops[k] = counters[2 + k];
     stats->kernel_launches = launches;
     stats->traversal_used = ctx->packed.traversal_used;
     stats->grid_blocks = ctx->last_launch.grid; stats->block_threads = ctx->last_launch.block;

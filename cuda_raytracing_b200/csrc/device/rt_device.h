@@ -77,7 +77,7 @@ struct RenderArgs {
   Scene scene;
   float *pixels;                // img_width*img_height*3 f32 (device)
   const uint32_t *rng_states;   // 6 words per pixel of the rendered row range: {d, v0..v4}
-  unsigned long long *counters; // [0] next work item, [1] rays traced
+  unsigned long long *counters; // [0] next work item, [1] rays traced, [2..13] operation counters (count_ops)
   int32_t img_width, img_height, samples_per_pixel, max_bounces;
   int32_t first_pixel, pixel_count;   // rendered range (row_begin*W .. row_end*W)
   float defocus_angle;
@@ -85,6 +85,7 @@ struct RenderArgs {
   float dv[3], du[3], cam[3], ddu[3], ddv[3], p00[3];
   float sample_scale;           // 1/spp, or 1 with RT_RENDER_OUTPUT_SUM
   uint32_t count_rays;
+  uint32_t count_ops;            // run the instrumented kernel variant (per-ray operation counts for F_ray)
 };
 
 constexpr int STACK_CAPACITY = 32;     // traversal stack entries per thread (shared memory, [slot][thread])

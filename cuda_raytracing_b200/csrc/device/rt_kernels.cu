@@ -17,6 +17,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <type_traits>
+
 #include "rt_device.h"
 #include "rt_math.cuh"
 #include "rt_shade.cuh"
@@ -40,14 +42,20 @@ __device__ __forceinline__ void stage_perlin(const Scene &sc, PerlinSmem *dst) {
   }
 }
 
-template <int MODE>
-__device__ __forceinline__ bool trace(const Scene &sc, Ray &r, Hit &h, uint32_t *stk, int stride) {
-  const float inf = __uint_as_float(0x7f800000u);
-  if (MODE == 0) return rtt::trace_reference(sc, r, 0.001f, inf, h, stk, stride);
-  return rtt::trace_fast(sc, r, 0.001f, inf, h, stk, stride);
+__device__ __forceinline__ void count_values(const rtt::NoCount &, unsigned long long *v) { for (int k = 0; k < 12; ++k) v[k] = 0; }
+__device__ __forceinline__ void count_values(const rtt::OpCount &c, unsigned long long *v) {
+  for (int k = 0; k < 12; ++k) v[k] = 0;
+  v[0] = c.n_box; v[1] = c.n_sphere; v[2] = c.n_planar; v[3] = c.n_translation; v[4] = c.n_rotation;
 }
 
-template <int MODE, int MAXB>
+template <int MODE, class C>
+__device__ __forceinline__ bool trace(const Scene &sc, Ray &r, Hit &h, uint32_t *stk, int stride, C &cnt) {
+  const float inf = __uint_as_float(0x7f800000u);
+  if (MODE == 0) return rtt::trace_reference(sc, r, 0.001f, inf, h, stk, stride, cnt);
+  return rtt::trace_fast(sc, r, 0.001f, inf, h, stk, stride, cnt);
+}
+
+template <int MODE, int MAXB, bool COUNT>
 __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) render_kernel(const RenderArgs a) {
   extern __shared__ __align__(16) uint32_t smem[];
   const Scene &sc = a.scene;
@@ -76,6 +84,8 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) render_kernel(const R
   Ray ray; ray.o = cam; ray.d = cam; ray.time = 0.0f;
   V3 base = cam, acc = v3(0.0f, 0.0f, 0.0f);
   unsigned long long rays = 0;
+  typename std::conditional<COUNT, rtt::OpCount, rtt::NoCount>::type cnt;
+  unsigned long long shade[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // COUNT only: lambert, metal, glass, light, noise, checker, arena, 0
 
   for (;;) {
     // ---- claim pixels for idle lanes: one atomic per warp ----
@@ -137,8 +147,13 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) render_kernel(const R
     if (!done) {
       ++rays;
       Hit h; h.u = 0.0f; h.v = 0.0f; h.t = 0.0f; h.prim = 0; h.front = 0; h.p = cam; h.n = cam;
-      if (trace<MODE>(sc, ray, h, stk, stride)) {
+      if (trace<MODE>(sc, ray, h, stk, stride, cnt)) {
         const uint4 m0 = __ldg(sc.materials + 2 * h.prim);
+        if (COUNT) {
+          const uint32_t ty = m0.x & 0xffu, tk = (m0.x >> 8) & 0xffu;
+          ++shade[ty & 3];
+          if (ty == rtd::M_LAMBERTIAN || ty == rtd::M_DIFFUSE_LIGHT) { if (tk == rtd::TK_NOISE) ++shade[4]; else if (tk == rtd::TK_CHECKER_SOLID) ++shade[5]; else if (tk == rtd::TK_ARENA) ++shade[6]; }
+        }
         const float4 m1 = __ldg(reinterpret_cast<const float4 *>(sc.materials + 2 * h.prim + 1));
         const V3 U = rng_unit_vector(rng);               // rt.cu:500-501: drawn for EVERY hit, whatever the material
         const float rtest = rng_uniform(rng);
@@ -177,6 +192,16 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) render_kernel(const R
   if (a.count_rays) {                                    // warp-aggregated ray counter
     for (int o = 16; o > 0; o >>= 1) rays += __shfl_xor_sync(full, rays, o);
     if (lane == 0) atomicAdd(a.counters + 1, rays);
+  }
+  if (COUNT) {                                           // operation counters -> counters[2..13]
+    unsigned long long v[12];
+    count_values(cnt, v);
+    for (int k = 0; k < 7; ++k) v[5 + k] = shade[k];
+    for (int k = 0; k < 12; ++k) {
+      unsigned long long x = v[k];
+      for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(full, x, o);
+      if (lane == 0) atomicAdd(a.counters + 2 + k, x);
+    }
   }
 }
 
@@ -299,8 +324,9 @@ __global__ void __launch_bounds__(PROBE_BLOCK) probe_trace_kernel(const Scene sc
   r.time = times ? times[i] : 0.0f;
   Hit h; h.u = 0.0f; h.v = 0.0f; h.t = 0.0f; h.prim = 0; h.front = 0; h.p = v3(0, 0, 0); h.n = v3(0, 0, 0);
   bool hit;
-  if (MODE == 0) hit = rtt::trace_reference(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x);
-  else hit = rtt::trace_fast(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x);
+  rtt::NoCount cnt;
+  if (MODE == 0) hit = rtt::trace_reference(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
+  else hit = rtt::trace_fast(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
   rt_probe_hit o;
   o.origin[0] = r.o.x; o.origin[1] = r.o.y; o.origin[2] = r.o.z;
   o.direction[0] = r.d.x; o.direction[1] = r.d.y; o.direction[2] = r.d.z;
@@ -371,11 +397,11 @@ cudaError_t launch_probe_texture(const rtd::Scene &scene, uint64_t n, uint32_t t
 // launch_render: persistent grid = SMs x resident blocks per SM (occupancy API), so every SM is full and the
 // work queue does the load balancing.
 // ======================================================================================================
-template <int MODE, int MAXB>
+template <int MODE, int MAXB, bool COUNT>
 static cudaError_t launch_render_t(const RenderArgs &args, int sm_count, cudaStream_t stream, LaunchInfo *info) {
   size_t smem = sizeof(uint32_t) * rtd::STACK_CAPACITY * RT_BLOCK;
   if (args.scene.perlin_tables > 0) smem += sizeof(PerlinSmem);
-  auto kernel = render_kernel<MODE, MAXB>;
+  auto kernel = render_kernel<MODE, MAXB, COUNT>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 50);
@@ -399,8 +425,12 @@ static cudaError_t launch_render_t(const RenderArgs &args, int sm_count, cudaStr
 
 cudaError_t launch_render(const rtd::RenderArgs &args, int mode, int sm_count, cudaStream_t stream, LaunchInfo *info) {
   const bool small = (args.max_bounces & 255) <= 64;
-  if (mode == 0) return small ? launch_render_t<0, 64>(args, sm_count, stream, info) : launch_render_t<0, 256>(args, sm_count, stream, info);
-  return small ? launch_render_t<1, 64>(args, sm_count, stream, info) : launch_render_t<1, 256>(args, sm_count, stream, info);
+  if (args.count_ops) {                                  // instrumented build of the same kernel (not the timed one)
+    if (mode == 0) return launch_render_t<0, 256, true>(args, sm_count, stream, info);
+    return launch_render_t<1, 256, true>(args, sm_count, stream, info);
+  }
+  if (mode == 0) return small ? launch_render_t<0, 64, false>(args, sm_count, stream, info) : launch_render_t<0, 256, false>(args, sm_count, stream, info);
+  return small ? launch_render_t<1, 64, false>(args, sm_count, stream, info) : launch_render_t<1, 256, false>(args, sm_count, stream, info);
 }
 
 }  // namespace rtk

@@ -23,6 +23,23 @@ struct Hit {
 
 __device__ __forceinline__ float4 ldg4(const float4 *p) { return __ldg(p); }
 
+// Per-ray operation counters for the roofline's F_ray; NoCount compiles to nothing.
+struct NoCount {
+  __device__ __forceinline__ void box(int) {}
+  __device__ __forceinline__ void sphere() {}
+  __device__ __forceinline__ void planar() {}
+  __device__ __forceinline__ void translation() {}
+  __device__ __forceinline__ void rotation() {}
+};
+struct OpCount {
+  unsigned long long n_box = 0, n_sphere = 0, n_planar = 0, n_translation = 0, n_rotation = 0;
+  __device__ __forceinline__ void box(int k) { n_box += k; }
+  __device__ __forceinline__ void sphere() { ++n_sphere; }
+  __device__ __forceinline__ void planar() { ++n_planar; }
+  __device__ __forceinline__ void translation() { ++n_translation; }
+  __device__ __forceinline__ void rotation() { ++n_rotation; }
+};
+
 // ---- sphere (rt.cu:1093-1123): a = d.d is passed in (it only changes when a wrapper rotates the ray) ----
 __device__ __forceinline__ bool hit_sphere(const Scene &sc, uint32_t idx, const Ray &r, float a, float tmin, float &tmax,
                                            Hit &h) {
@@ -100,9 +117,9 @@ __device__ __forceinline__ bool aabb_axis(float lo, float hi, float o, float inv
 // ================= reference-order traversal (instance wrappers, reference BVH, reference visiting order) ======
 // Returns true when something was hit.  The ray is edited in place by the wrappers and, like the reference,
 // comes back with the rounding drift of the un-rotate / un-translate (Q12).
-template <int STRIDE_IS_BLOCKDIM = 1>
+template <class C>
 __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float tmin, float tmax, Hit &h,
-                                                uint32_t *stk, const int stride) {
+                                                uint32_t *stk, const int stride, C &cnt) {
   bool result = false, was_last_hit = false, in_translation = false, in_rotation = false;
   int sp = 0;
   stk[0] = sc.ref_root; sp = 1;
@@ -113,10 +130,12 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
     const uint32_t idx = rtd::ref_index(cur);
     switch (rtd::ref_kind(cur)) {
       case rtd::K_SPHERE:
+        cnt.sphere();
         if (hit_sphere(sc, idx, r, a, tmin, tmax, h)) { result = true; if (in_translation || in_rotation) was_last_hit = true; }
         break;
       case rtd::K_TRIANGLE:
       case rtd::K_QUAD:
+        cnt.planar();
         if (hit_planar(sc, idx, rtd::ref_kind(cur) == rtd::K_TRIANGLE, r, tmin, tmax, h)) {
           result = true; if (in_translation || in_rotation) was_last_hit = true;
         }
@@ -125,6 +144,7 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
         const float4 n0 = ldg4(sc.ref_nodes + 2 * idx);
         const float4 n1 = ldg4(sc.ref_nodes + 2 * idx + 1);
         float t0 = tmin, t1 = tmax;
+        cnt.box(1);
         if (aabb_axis(n0.x, n0.y, r.o.x, inv.x, t0, t1) && aabb_axis(n0.z, n0.w, r.o.y, inv.y, t0, t1) &&
             aabb_axis(n1.x, n1.y, r.o.z, inv.z, t0, t1)) {
           stk[(sp++) * stride] = __float_as_uint(n1.w);    // right first => left is visited first (Q11)
@@ -134,6 +154,7 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
       case rtd::K_TRANSLATION: {
         const float4 x = ldg4(sc.xforms + idx);
         const V3 off = v3(x.x, x.y, x.z);
+        cnt.translation();
         if (!in_translation) {
           was_last_hit = false;
           r.o = vsub(r.o, off);
@@ -149,6 +170,7 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
       case rtd::K_YROTATION: {
         const float4 x = ldg4(sc.xforms + idx);
         const float sn = x.x, cs = x.y;
+        cnt.rotation();
         if (!in_rotation) {                                 // rt.cu:1194-1209, roundings from the reference's SASS
           was_last_hit = false;
           const V3 o = r.o, d = r.d;
@@ -184,8 +206,9 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
 // ================= own BVH (SAH, world-space primitives, near child first) =====================================
 // Closest hit is independent of visiting order and of (conservative) box culling, so for scenes without
 // instance wrappers this returns bit-identical hits to trace_reference at a fraction of the node visits.
+template <class C>
 __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float tmin, float tmax, Hit &h,
-                                           uint32_t *stk, const int stride) {
+                                           uint32_t *stk, const int stride, C &cnt) {
   bool result = false;
   const V3 inv = v3(frcp(r.d.x), frcp(r.d.y), frcp(r.d.z));
   const float a = dot_xfirst(r.d, r.d);
@@ -199,6 +222,7 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
       const float4 n1 = ldg4(sc.fast_nodes + 4 * idx + 1);
       const float4 n2 = ldg4(sc.fast_nodes + 4 * idx + 2);
       const float4 n3 = ldg4(sc.fast_nodes + 4 * idx + 3);
+      cnt.box(2);
       // slab test of both children; fminf/fmaxf drop NaNs (0*inf) which keeps the test conservative
       const float c0x0 = (n0.x - r.o.x) * inv.x, c0x1 = (n0.y - r.o.x) * inv.x;
       const float c0y0 = (n0.z - r.o.y) * inv.y, c0y1 = (n0.w - r.o.y) * inv.y;
@@ -222,8 +246,10 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
         continue;
       }
     } else if (kind == rtd::K_SPHERE) {
+      cnt.sphere();
       result |= hit_sphere(sc, idx, r, a, tmin, tmax, h);
     } else if (kind == rtd::K_QUAD || kind == rtd::K_TRIANGLE) {
+      cnt.planar();
       result |= hit_planar(sc, idx, kind == rtd::K_TRIANGLE, r, tmin, tmax, h);
     }                                                     // K_NONE: the empty second child of a one-primitive scene
     if (sp == 0) break;

@@ -36,8 +36,10 @@ typedef struct rt_context rt_context;
 int  rt_context_create(int device_id, rt_context **out);
 void rt_context_destroy(rt_context *ctx);                 /* frees every device allocation (the reference never does) */
 const char *rt_last_error_string(const rt_context *ctx);  /* ctx may be NULL: last global error */
-/* use the caller's CUDA stream (cudaStream_t passed as void*; NULL = the context's own stream) */
+/* enqueue on the caller's CUDA stream (cudaStream_t passed as void*; NULL is the CUDA default stream, which is
+ * what the reference uses); rt_context_reset_stream() goes back to the context's own non-blocking stream */
 int  rt_context_set_stream(rt_context *ctx, void *cuda_stream);
+int  rt_context_reset_stream(rt_context *ctx);
 
 /* ---- scene upload: replaces the 4 cudaMalloc+cudaMemcpy blocks of render() (rt.cu:1699-1733) ----
  * Input is the reference's own scene format AFTER make_bvh(): Hittable[120 B], u16 world refs (prims
@@ -65,8 +67,12 @@ int rt_scene_upload(rt_context *ctx, const rt_scene_desc *scene, uint32_t traver
 enum {
   RT_RENDER_OUTPUT_SUM = 1u,      /* leave the per-pixel SUM over samples (for multi-GPU sample sharding + reduce) */
   RT_RENDER_NO_RNG_CACHE = 2u,    /* recompute the XORWOW states even if cached from the previous call */
-  RT_RENDER_COUNT_RAYS = 4u       /* fill rt_stats.rays (warp-aggregated counter; small cost) */
+  RT_RENDER_COUNT_RAYS = 4u,      /* fill rt_stats.rays (warp-aggregated counter; small cost) */
+  RT_RENDER_COUNT_OPS = 8u        /* instrumented kernel variant: fill rt_stats.ops (never use for timing) */
 };
+/* per-render operation totals of the instrumented variant; index names below */
+enum { RT_OP_BOX = 0, RT_OP_SPHERE, RT_OP_PLANAR, RT_OP_TRANSLATION, RT_OP_ROTATION, RT_OP_LAMBERT, RT_OP_METAL, RT_OP_GLASS,
+       RT_OP_LIGHT, RT_OP_NOISE, RT_OP_CHECKER, RT_OP_ARENA, RT_OP_COUNT };
 typedef struct rt_render_params {
   int32_t img_width, img_height;
   int32_t samples_per_pixel, max_bounces;
@@ -87,6 +93,7 @@ typedef struct rt_stats {
   uint32_t kernel_launches;
   uint32_t traversal_used;                     /* RT_TRAVERSAL_REFERENCE or RT_TRAVERSAL_FAST */
   uint32_t grid_blocks, block_threads, regs_per_thread, blocks_per_sm;
+  uint64_t ops[12];                            /* RT_RENDER_COUNT_OPS only */
 } rt_stats;
 
 void rt_render_params_from_camera(const rt_render_settings *s, const rt_camera *c, rt_render_params *p);
