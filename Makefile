@@ -1,8 +1,8 @@
 # Builds the product: libraytracing_b200.so (host C + CUDA sm_100a, C ABI of include/rt_api.h) and bin/raytracing.
 # `make oracle` builds the CPU oracle (test infrastructure), `make ref` the real reference into oracle/_ref/.
 NVCC ?= nvcc
-CC ?= gcc
-CXX ?= g++
+CC := gcc
+CXX := g++
 PKG := cuda_raytracing_b200
 DEV := $(PKG)/csrc/device
 HOST := $(PKG)/csrc/host
