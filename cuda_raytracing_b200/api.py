@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libraytracing_b200.so")
+LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "libraytracing_b200.so")   # env: kernel-variant experiments
 
 RT_TRAVERSAL_AUTO, RT_TRAVERSAL_REFERENCE, RT_TRAVERSAL_FAST = 0, 1, 2
 RT_RENDER_OUTPUT_SUM, RT_RENDER_NO_RNG_CACHE, RT_RENDER_COUNT_RAYS, RT_RENDER_COUNT_OPS = 1, 2, 4, 8

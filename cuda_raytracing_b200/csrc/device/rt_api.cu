@@ -4,6 +4,7 @@
 
 #include <cuda_runtime.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <chrono>
@@ -58,7 +59,9 @@ struct rt_context {
   DeviceBuffer b_ref_nodes, b_xforms, b_structs, b_struct_children, b_fast_nodes, b_spheres, b_planars, b_materials,
       b_checkers, b_perlin_vec, b_perlin_perm, b_arena;
   // rng
-  DeviceBuffer b_rng_mats, b_rng_states, b_counters;
+  DeviceBuffer b_rng_mats, b_rng_init, b_rng_states, b_progress, b_counters;   // b_rng_init: pristine states (cache)
+  int chunk_samples = 0;                                   // 0 = automatic; env RT_CHUNK overrides (tuning knob)
+  int claim_group = 0;                                     // 0 = automatic; env RT_CLAIM_GROUP (tuning knob)
   uint64_t rng_seed = 0, rng_first = 0, rng_count = 0; bool rng_valid = false;
   // scratch for rt_render (host-buffer path)
   DeviceBuffer b_pixels, b_rgb8;
@@ -98,6 +101,8 @@ int rt_context_create(int device_id, rt_context **out) {
   if (e != cudaSuccess) { delete ctx; return cuda_fail(nullptr, e, "cudaStreamCreate"); }
   ctx->stream = ctx->own_stream;
   for (int i = 0; i < 4; ++i) cudaEventCreate(&ctx->ev[i]);
+  if (const char *v = getenv("RT_CHUNK")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 24)) ctx->chunk_samples = (int)x; }
+  if (const char *v = getenv("RT_CLAIM_GROUP")) { const long x = strtol(v, nullptr, 10); if (x >= 1 && x <= 32) ctx->claim_group = (int)x; }
   std::vector<uint32_t> mats;
   rtp::xorwow_sequence_matrices(mats);
   e = ctx->b_rng_mats.upload(mats.data(), mats.size() * sizeof(uint32_t), ctx->stream);
@@ -114,7 +119,8 @@ void rt_context_destroy(rt_context *ctx) {
   cudaStreamSynchronize(ctx->stream);
   DeviceBuffer *all[] = {&ctx->b_ref_nodes, &ctx->b_xforms, &ctx->b_structs, &ctx->b_struct_children, &ctx->b_fast_nodes,
                          &ctx->b_spheres, &ctx->b_planars, &ctx->b_materials, &ctx->b_checkers, &ctx->b_perlin_vec,
-                         &ctx->b_perlin_perm, &ctx->b_arena, &ctx->b_rng_mats, &ctx->b_rng_states, &ctx->b_counters,
+                         &ctx->b_perlin_perm, &ctx->b_arena, &ctx->b_rng_mats, &ctx->b_rng_init, &ctx->b_rng_states,
+                         &ctx->b_progress, &ctx->b_counters,
                          &ctx->b_pixels, &ctx->b_rgb8};
   for (DeviceBuffer *b : all) b->release();
   for (int i = 0; i < 4; ++i) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
@@ -198,20 +204,45 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   const bool cached = ctx->rng_valid && ctx->rng_seed == p->seed && ctx->rng_first == first_sub && ctx->rng_count == count &&
                       !(p->flags & RT_RENDER_NO_RNG_CACHE);
   if (!cached) {
-    RT_CUDA(ctx, ctx->b_rng_states.reserve(count * 6 * sizeof(uint32_t)));
+    RT_CUDA(ctx, ctx->b_rng_init.reserve(count * 6 * sizeof(uint32_t)));
     RT_CUDA(ctx, rtk::launch_rng_init(p->seed, first_sub, count, (const uint32_t *)ctx->b_rng_mats.ptr,
-                                      (uint32_t *)ctx->b_rng_states.ptr, s));
+                                      (uint32_t *)ctx->b_rng_init.ptr, s));
     ctx->rng_seed = p->seed; ctx->rng_first = first_sub; ctx->rng_count = count; ctx->rng_valid = true;
     ++launches;
   }
-  if (stats) RT_CUDA(ctx, cudaEventRecord(ctx->ev[1], s));
+  // the render kernel advances the states chunk by chunk: it works on a copy, the initial states stay cached
+  RT_CUDA(ctx, ctx->b_rng_states.reserve(count * 6 * sizeof(uint32_t)));
+  RT_CUDA(ctx, ctx->b_progress.reserve(count * sizeof(uint32_t)));
+  RT_CUDA(ctx, cudaMemcpyAsync(ctx->b_rng_states.ptr, ctx->b_rng_init.ptr, count * 6 * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+  RT_CUDA(ctx, cudaMemsetAsync(ctx->b_progress.ptr, 0, count * sizeof(uint32_t), s));
   RT_CUDA(ctx, cudaMemsetAsync(ctx->b_counters.ptr, 0, 16 * sizeof(unsigned long long), s));
+  if (stats) RT_CUDA(ctx, cudaEventRecord(ctx->ev[1], s));
 
   rtd::RenderArgs a;
   memset(&a, 0, sizeof(a));
   a.scene = ctx->scene;
   a.pixels = d_pixels;
-  a.rng_states = (const uint32_t *)ctx->b_rng_states.ptr;
+  a.rng_states = (uint32_t *)ctx->b_rng_states.ptr;
+  a.progress = (uint32_t *)ctx->b_progress.ptr;
+  {   // chunk size: about 1/32 of the samples one resident lane will produce, so that the tail of the render (lanes
+      // idle because every remaining pixel is owned) is a few per cent; never below 8 samples per claim
+    const int spp = p->samples_per_pixel > 0 ? p->samples_per_pixel : 1;
+    int chunk = ctx->chunk_samples;
+    if (chunk <= 0) {
+      const double lanes = (double)ctx->sm_count * 640.0;
+      const double per_lane = (double)spp * (double)count / lanes;
+      chunk = (int)(per_lane / 32.0);
+      if (chunk < 8) chunk = 8;
+    }
+    if (chunk > spp) chunk = spp;
+    a.chunk_samples = chunk;
+    a.chunk_count = (spp + chunk - 1) / chunk;
+    a.item_count = (unsigned long long)count * (unsigned long long)a.chunk_count;
+    // measured (profiles/r1_sweep_chunk_group.jsonl): big own-BVH scenes gain from claiming a whole warp of adjacent
+    // pixels at once (coherent node visits), small scenes and the reference-order walk from claiming at once
+    const bool big_fast = ctx->packed.traversal_used == RT_TRAVERSAL_FAST && ctx->packed.sphere_count + ctx->packed.planar_count >= 64;
+    a.claim_group = ctx->claim_group > 0 ? ctx->claim_group : (big_fast ? 32 : 1);
+  }
   a.counters = (unsigned long long *)ctx->b_counters.ptr;
   a.img_width = p->img_width; a.img_height = p->img_height;
   a.samples_per_pixel = p->samples_per_pixel; a.max_bounces = p->max_bounces;

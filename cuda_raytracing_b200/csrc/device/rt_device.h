@@ -76,8 +76,12 @@ struct Scene {
 struct RenderArgs {
   Scene scene;
   float *pixels;                // img_width*img_height*3 f32 (device)
-  const uint32_t *rng_states;   // 6 words per pixel of the rendered row range: {d, v0..v4}
+  uint32_t *rng_states;         // 6 words per pixel of the rendered row range: {d, v0..v4}; advanced chunk by chunk
+  uint32_t *progress;           // per pixel of the range: chunks completed (zeroed before the launch)
   unsigned long long *counters; // [0] next work item, [1] rays traced, [2..13] operation counters (count_ops)
+  unsigned long long item_count;// pixel_count * chunk_count work items; item = chunk * pixel_count + pixel
+  int32_t chunk_samples, chunk_count;   // a pixel's samples are produced in order, chunk_samples at a time
+  int32_t claim_group;          // idle lanes of a warp claim work items together, this many at a time
   int32_t img_width, img_height, samples_per_pixel, max_bounces;
   int32_t first_pixel, pixel_count;   // rendered range (row_begin*W .. row_end*W)
   float defocus_angle;

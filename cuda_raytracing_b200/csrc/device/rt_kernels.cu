@@ -33,7 +33,10 @@ using rtt::Hit;
 using rtt::Ray;
 
 constexpr int RT_BLOCK = 128;
-constexpr int RT_MIN_BLOCKS = 5;
+#ifndef RT_MIN_BLOCKS_PER_SM
+#define RT_MIN_BLOCKS_PER_SM 5                          // 5 x 128 threads x 96 registers (tools/build_variants.sh sweeps it)
+#endif
+constexpr int RT_MIN_BLOCKS = RT_MIN_BLOCKS_PER_SM;
 
 __device__ __forceinline__ void stage_perlin(const Scene &sc, PerlinSmem *dst) {
   for (int i = threadIdx.x; i < 256; i += blockDim.x) {
@@ -47,6 +50,9 @@ __device__ __forceinline__ void count_values(const rtt::OpCount &c, unsigned lon
   for (int k = 0; k < 12; ++k) v[k] = 0;
   v[0] = c.n_box; v[1] = c.n_sphere; v[2] = c.n_planar; v[3] = c.n_translation; v[4] = c.n_rotation;
 }
+
+__device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t *p) { return *reinterpret_cast<const volatile uint32_t *>(p); }
+__device__ __forceinline__ void st_volatile_u32(uint32_t *p, uint32_t v) { *reinterpret_cast<volatile uint32_t *>(p) = v; }
 
 template <int MODE, class C>
 __device__ __forceinline__ bool trace(const Scene &sc, Ray &r, Hit &h, uint32_t *stk, int stride, C &cnt) {
@@ -77,8 +83,12 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) render_kernel(const R
 
   float att_r[MAXB], att_g[MAXB], att_b[MAXB];         // thread-local attenuation stack (unwound backwards)
 
-  int pix = -1;
-  bool exhausted = false, new_path = false;
+  // Work item = (chunk of `chunk_samples` samples, pixel), handed out chunk-major: item = chunk * pixel_count + pixel.
+  // A pixel's samples are produced strictly in order from its own XORWOW state (that is the reference's stream),
+  // but not necessarily by one lane: between chunks the state and the running sum are parked in global memory,
+  // so the tail of a render is one chunk long instead of one pixel long (parallelism = pixels).
+  int pix = -1, chunk = 0;                               // pix: index inside the rendered range
+  bool exhausted = false, new_path = false, waiting = false;
   int samples_left = 0, budget = 0, depth = 0;
   Rng rng = {0, 0, 0, 0, 0, 0};
   Ray ray; ray.o = cam; ray.d = cam; ray.time = 0.0f;
@@ -88,40 +98,51 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) render_kernel(const R
   unsigned long long shade[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // COUNT only: lambert, metal, glass, light, noise, checker, arena, 0
 
   for (;;) {
-    // ---- claim pixels for idle lanes: one atomic per warp ----
+    // ---- claim work items for idle lanes: one atomic per warp ----
+    // Lanes claim together, `claim_group` at a time (fewer only when the rest of the warp has nothing to do): items
+    // claimed together are adjacent pixels, whose rays visit the same nodes (coherence), at the price of a short wait.
     const bool want = (pix < 0) && !exhausted;
     const unsigned m = __ballot_sync(full, want);
-    if (m) {
+    if (m && (__popc(m) >= a.claim_group || __popc(m) + __popc(__ballot_sync(full, exhausted)) == 32)) {
       const int leader = __ffs(m) - 1;
       unsigned long long first = 0;
       if ((int)lane == leader) first = atomicAdd(a.counters, (unsigned long long)__popc(m));
       first = __shfl_sync(full, first, leader);
       if (want) {
         const unsigned long long item = first + __popc(m & ((1u << lane) - 1u));
-        if (item < (unsigned long long)a.pixel_count) {
-          pix = a.first_pixel + (int)item;
-          const uint2 *st = reinterpret_cast<const uint2 *>(a.rng_states) + 3 * (size_t)item;
-          const uint2 s0 = __ldg(st), s1 = __ldg(st + 1), s2 = __ldg(st + 2);
-          rng.d = s0.x; rng.v0 = s0.y; rng.v1 = s1.x; rng.v2 = s1.y; rng.v3 = s2.x; rng.v4 = s2.y;
-          const int j = pix % a.img_width, i = (pix - j) / a.img_width;     // rt.cu:1561-1567
-          const float fi = (float)i, fj = (float)j;
-          base = v3(fadd(ffma(fj, du.x, fmul(fi, dv.x)), a.p00[0]), fadd(ffma(fj, du.y, fmul(fi, dv.y)), a.p00[1]),
-                    fadd(ffma(fj, du.z, fmul(fi, dv.z)), a.p00[2]));
-          acc = v3(0.0f, 0.0f, 0.0f);
-          samples_left = a.samples_per_pixel;
-          new_path = true;
-          if (samples_left <= 0) {                      // spp <= 0: the reference writes 0 * scale
-            float *out = a.pixels + 3 * (size_t)pix;
-            out[0] = 0.0f; out[1] = 0.0f; out[2] = 0.0f;
-            pix = -1;
-          }
+        if (item < a.item_count) {
+          chunk = (int)(item / (unsigned long long)a.pixel_count);
+          pix = (int)(item - (unsigned long long)chunk * (unsigned long long)a.pixel_count);
+          waiting = true;
         } else {
           exhausted = true;
         }
       }
     }
+    if (waiting && (chunk == 0 || ld_volatile_u32(a.progress + pix) >= (uint32_t)chunk)) {
+      // chunk k of a pixel starts from the state chunk k-1 left behind (ordered by the fence + progress counter)
+      waiting = false;
+      if (chunk != 0) __threadfence();
+      const uint2 *st = reinterpret_cast<const uint2 *>(a.rng_states) + 3 * (size_t)pix;
+      const uint2 s0 = __ldcg(st), s1 = __ldcg(st + 1), s2 = __ldcg(st + 2);
+      rng.d = s0.x; rng.v0 = s0.y; rng.v1 = s1.x; rng.v2 = s1.y; rng.v3 = s2.x; rng.v4 = s2.y;
+      const int gp = a.first_pixel + pix;
+      float *out = a.pixels + 3 * (size_t)gp;
+      acc = chunk ? v3(__ldcg(out), __ldcg(out + 1), __ldcg(out + 2)) : v3(0.0f, 0.0f, 0.0f);
+      const int j = gp % a.img_width, i = (gp - j) / a.img_width;     // rt.cu:1561-1567
+      const float fi = (float)i, fj = (float)j;
+      base = v3(fadd(ffma(fj, du.x, fmul(fi, dv.x)), a.p00[0]), fadd(ffma(fj, du.y, fmul(fi, dv.y)), a.p00[1]),
+                fadd(ffma(fj, du.z, fmul(fi, dv.z)), a.p00[2]));
+      const int done = chunk * a.chunk_samples;
+      samples_left = a.samples_per_pixel - done < a.chunk_samples ? a.samples_per_pixel - done : a.chunk_samples;
+      new_path = true;
+      if (samples_left <= 0) {                      // spp <= 0: the reference writes 0 * scale
+        out[0] = 0.0f; out[1] = 0.0f; out[2] = 0.0f;
+        pix = -1;
+      }
+    }
     if (!__any_sync(full, pix >= 0)) break;
-    if (pix < 0) continue;
+    if (pix < 0 || waiting) continue;
 
     // ---- (1) camera ray generation (rt.cu:1570-1578) ----
     if (new_path) {
@@ -175,15 +196,22 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) render_kernel(const R
 
     // ---- (5) unwind, accumulate, resolve ----
     if (done) {
+      if (result.x == 0.0f && result.y == 0.0f && result.z == 0.0f) depth = 0;   // 0 stays +0 through every fma(0, att, 0)
       while (depth > 0) {                                // result = att (.) result + emission, one fma per channel
         --depth;
         result = v3(ffma(result.x, att_r[depth], 0.0f), ffma(result.y, att_g[depth], 0.0f), ffma(result.z, att_b[depth], 0.0f));
       }
       acc = vadd(acc, result);
       new_path = true;
-      if (--samples_left == 0) {
-        float *out = a.pixels + 3 * (size_t)pix;
-        out[0] = fmul(a.sample_scale, acc.x); out[1] = fmul(a.sample_scale, acc.y); out[2] = fmul(a.sample_scale, acc.z);
+      if (--samples_left == 0) {                         // chunk done: final value, or running sum + state for the next owner
+        float *out = a.pixels + 3 * ((size_t)a.first_pixel + (size_t)pix);
+        uint2 *st = reinterpret_cast<uint2 *>(a.rng_states + 6 * (size_t)pix);
+        const bool last = (chunk + 1 == a.chunk_count);
+        __stcg(out, last ? fmul(a.sample_scale, acc.x) : acc.x);
+        __stcg(out + 1, last ? fmul(a.sample_scale, acc.y) : acc.y);
+        __stcg(out + 2, last ? fmul(a.sample_scale, acc.z) : acc.z);
+        __stcg(st, make_uint2(rng.d, rng.v0)); __stcg(st + 1, make_uint2(rng.v1, rng.v2)); __stcg(st + 2, make_uint2(rng.v3, rng.v4));
+        if (!last) { __threadfence(); st_volatile_u32(a.progress + pix, (uint32_t)(chunk + 1)); }
         pix = -1;
       }
     }

@@ -210,8 +210,15 @@ template <class C>
 __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float tmin, float tmax, Hit &h,
                                            uint32_t *stk, const int stride, C &cnt) {
   bool result = false;
-  const V3 inv = v3(frcp(r.d.x), frcp(r.d.y), frcp(r.d.z));
   const float a = dot_xfirst(r.d, r.d);
+  // slab planes as one fma each: t = plane * inv - o * inv.  The rounding of o * inv moves a plane by up to
+  // |o * inv| * 2^-24 in t, so the overlap test gets 8x that much slack (and a relative one for the fma itself):
+  // the cull stays conservative, which is all that exactness of the closest hit needs.  1/d is clamped to a
+  // finite value so that a ray parallel to a slab gets -huge/+huge plane distances instead of inf - inf.
+  const float big = 1.0e30f;
+  const V3 inv = v3(fminf(fmaxf(frcp(r.d.x), -big), big), fminf(fmaxf(frcp(r.d.y), -big), big), fminf(fmaxf(frcp(r.d.z), -big), big));
+  const V3 noi = v3(-(r.o.x * inv.x), -(r.o.y * inv.y), -(r.o.z * inv.z));
+  const float slack = fminf((fabsf(noi.x) + fabsf(noi.y) + fabsf(noi.z)) * 4.76837158e-7f, 3.0e38f);
   int sp = 0;
   uint32_t cur = sc.fast_root;
   for (;;) {
@@ -224,16 +231,17 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
       const float4 n3 = ldg4(sc.fast_nodes + 4 * idx + 3);
       cnt.box(2);
       // slab test of both children; fminf/fmaxf drop NaNs (0*inf) which keeps the test conservative
-      const float c0x0 = (n0.x - r.o.x) * inv.x, c0x1 = (n0.y - r.o.x) * inv.x;
-      const float c0y0 = (n0.z - r.o.y) * inv.y, c0y1 = (n0.w - r.o.y) * inv.y;
-      const float c0z0 = (n2.x - r.o.z) * inv.z, c0z1 = (n2.y - r.o.z) * inv.z;
-      const float c1x0 = (n1.x - r.o.x) * inv.x, c1x1 = (n1.y - r.o.x) * inv.x;
-      const float c1y0 = (n1.z - r.o.y) * inv.y, c1y1 = (n1.w - r.o.y) * inv.y;
-      const float c1z0 = (n2.z - r.o.z) * inv.z, c1z1 = (n2.w - r.o.z) * inv.z;
+      const float c0x0 = fmaf(n0.x, inv.x, noi.x), c0x1 = fmaf(n0.y, inv.x, noi.x);
+      const float c0y0 = fmaf(n0.z, inv.y, noi.y), c0y1 = fmaf(n0.w, inv.y, noi.y);
+      const float c0z0 = fmaf(n2.x, inv.z, noi.z), c0z1 = fmaf(n2.y, inv.z, noi.z);
+      const float c1x0 = fmaf(n1.x, inv.x, noi.x), c1x1 = fmaf(n1.y, inv.x, noi.x);
+      const float c1y0 = fmaf(n1.z, inv.y, noi.y), c1y1 = fmaf(n1.w, inv.y, noi.y);
+      const float c1z0 = fmaf(n2.z, inv.z, noi.z), c1z1 = fmaf(n2.w, inv.z, noi.z);
       const float e0 = fmaxf(fmaxf(fminf(c0x0, c0x1), fminf(c0y0, c0y1)), fmaxf(fminf(c0z0, c0z1), tmin));
-      const float x0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), tmax));
+      float x0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), tmax));
       const float e1 = fmaxf(fmaxf(fminf(c1x0, c1x1), fminf(c1y0, c1y1)), fmaxf(fminf(c1z0, c1z1), tmin));
-      const float x1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), tmax));
+      float x1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), tmax));
+      x0 = fmaf(x0, 1.000001f, slack); x1 = fmaf(x1, 1.000001f, slack);
       const bool h0 = e0 <= x0, h1 = e1 <= x1;
       const uint32_t r0 = __float_as_uint(n3.x), r1 = __float_as_uint(n3.y);
       if (h0 && h1) {
