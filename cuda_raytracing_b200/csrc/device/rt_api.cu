@@ -62,6 +62,7 @@ struct rt_context {
   DeviceBuffer b_rng_mats, b_rng_init, b_rng_states, b_progress, b_counters;   // b_rng_init: pristine states (cache)
   int chunk_samples = 0;                                   // 0 = automatic; env RT_CHUNK overrides (tuning knob)
   int claim_group = 0;                                     // 0 = automatic; env RT_CLAIM_GROUP (tuning knob)
+  int tile_w = 8;                                          // work items walk 8x4-pixel tiles; env RT_TILE_W (1..32, power of 2)
   uint64_t rng_seed = 0, rng_first = 0, rng_count = 0; bool rng_valid = false;
   // scratch for rt_render (host-buffer path)
   DeviceBuffer b_pixels, b_rgb8;
@@ -102,7 +103,8 @@ int rt_context_create(int device_id, rt_context **out) {
   ctx->stream = ctx->own_stream;
   for (int i = 0; i < 4; ++i) cudaEventCreate(&ctx->ev[i]);
   if (const char *v = getenv("RT_CHUNK")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 24)) ctx->chunk_samples = (int)x; }
-  if (const char *v = getenv("RT_CLAIM_GROUP")) { const long x = strtol(v, nullptr, 10); if (x >= 1 && x <= 32) ctx->claim_group = (int)x; }
+  if (const char *v = getenv("RT_TILE_W")) { const long x = strtol(v, nullptr, 10); if (x >= 1 && x <= 32 && (x & (x - 1)) == 0) ctx->tile_w = (int)x; }
+  if (const char *v = getenv("RT_CLAIM_GROUP")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= 32) ctx->claim_group = (int)x; }
   std::vector<uint32_t> mats;
   rtp::xorwow_sequence_matrices(mats);
   e = ctx->b_rng_mats.upload(mats.data(), mats.size() * sizeof(uint32_t), ctx->stream);
@@ -229,7 +231,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
     const int spp = p->samples_per_pixel > 0 ? p->samples_per_pixel : 1;
     int chunk = ctx->chunk_samples;
     if (chunk <= 0) {
-      const double lanes = (double)ctx->sm_count * 640.0;
+      const double lanes = (double)ctx->sm_count * (ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? 768.0 : 640.0);   // resident threads
       const double per_lane = (double)spp * (double)count / lanes;
       chunk = (int)(per_lane / 32.0);
       if (chunk < 8) chunk = 8;
@@ -237,7 +239,11 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
     if (chunk > spp) chunk = spp;
     a.chunk_samples = chunk;
     a.chunk_count = (spp + chunk - 1) / chunk;
-    a.item_count = (unsigned long long)count * (unsigned long long)a.chunk_count;
+    const uint32_t tw = (uint32_t)ctx->tile_w, th = 32u / tw, rows = (uint32_t)(row1 - row0);
+    a.tile_w = tw;
+    a.tiles_x = ((uint32_t)p->img_width + tw - 1) / tw;
+    a.slots_per_chunk = a.tiles_x * ((rows + th - 1) / th) * 32u;
+    a.item_count = (unsigned long long)a.slots_per_chunk * (unsigned long long)a.chunk_count;
     // measured (profiles/r1_sweep_chunk_group.jsonl): big own-BVH scenes gain from claiming a whole warp of adjacent
     // pixels at once (coherent node visits), small scenes and the reference-order walk from claiming at once
     const bool big_fast = ctx->packed.traversal_used == RT_TRAVERSAL_FAST && ctx->packed.sphere_count + ctx->packed.planar_count >= 64;

@@ -79,7 +79,9 @@ struct RenderArgs {
   uint32_t *rng_states;         // 6 words per pixel of the rendered row range: {d, v0..v4}; advanced chunk by chunk
   uint32_t *progress;           // per pixel of the range: chunks completed (zeroed before the launch)
   unsigned long long *counters; // [0] next work item, [1] rays traced, [2..13] operation counters (count_ops)
-  unsigned long long item_count;// pixel_count * chunk_count work items; item = chunk * pixel_count + pixel
+  unsigned long long item_count;// slots_per_chunk * chunk_count work items; item = chunk * slots_per_chunk + slot
+  uint32_t slots_per_chunk;     // 32 * number of 32-pixel tiles covering the rendered rows (>= pixel_count)
+  uint32_t tiles_x, tile_w;     // tiles per row of tiles; tile width in pixels (power of two <= 32, height = 32 / width)
   int32_t chunk_samples, chunk_count;   // a pixel's samples are produced in order, chunk_samples at a time
   int32_t claim_group;          // idle lanes of a warp claim work items together, this many at a time
   int32_t img_width, img_height, samples_per_pixel, max_bounces;

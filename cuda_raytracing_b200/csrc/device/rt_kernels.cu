@@ -33,10 +33,13 @@ using rtt::Hit;
 using rtt::Ray;
 
 constexpr int RT_BLOCK = 128;
-#ifndef RT_MIN_BLOCKS_PER_SM
-#define RT_MIN_BLOCKS_PER_SM 5                          // 5 x 128 threads x 96 registers (tools/build_variants.sh sweeps it)
+// resident blocks per SM asked of the compiler: 6 x 128 threads x 80 registers for the own-BVH walk, 5 x 96 for the
+// reference-order walk (measured both ways, profiles/r1_sweep_tile_occ.jsonl; tools/build_variants.sh overrides)
+#ifdef RT_MIN_BLOCKS_PER_SM
+constexpr int RT_MIN_BLOCKS_FAST = RT_MIN_BLOCKS_PER_SM, RT_MIN_BLOCKS_REF = RT_MIN_BLOCKS_PER_SM;
+#else
+constexpr int RT_MIN_BLOCKS_FAST = 6, RT_MIN_BLOCKS_REF = 5;
 #endif
-constexpr int RT_MIN_BLOCKS = RT_MIN_BLOCKS_PER_SM;
 
 __device__ __forceinline__ void stage_perlin(const Scene &sc, PerlinSmem *dst) {
   for (int i = threadIdx.x; i < 256; i += blockDim.x) {
@@ -62,7 +65,7 @@ __device__ __forceinline__ bool trace(const Scene &sc, Ray &r, Hit &h, uint32_t 
 }
 
 template <int MODE, int MAXB, bool COUNT>
-__global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) render_kernel(const RenderArgs a) {
+__global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_MIN_BLOCKS_REF) render_kernel(const RenderArgs a) {
   extern __shared__ __align__(16) uint32_t smem[];
   const Scene &sc = a.scene;
   uint32_t *stk = smem + threadIdx.x;
@@ -111,9 +114,17 @@ __global__ void __launch_bounds__(RT_BLOCK, RT_MIN_BLOCKS) render_kernel(const R
       if (want) {
         const unsigned long long item = first + __popc(m & ((1u << lane) - 1u));
         if (item < a.item_count) {
-          chunk = (int)(item / (unsigned long long)a.pixel_count);
-          pix = (int)(item - (unsigned long long)chunk * (unsigned long long)a.pixel_count);
-          waiting = true;
+          // items walk the range in tiles of 32 pixels (tile_w x 32/tile_w): a warp that claims together gets a compact
+          // block of the image, whose rays visit the same nodes.  Slots of a border tile that fall outside are no-ops.
+          chunk = (int)(item / (unsigned long long)a.slots_per_chunk);
+          const uint32_t slot = (uint32_t)(item - (unsigned long long)chunk * (unsigned long long)a.slots_per_chunk);
+          const uint32_t tile = slot >> 5, l = slot & 31u;
+          const uint32_t ty = tile / a.tiles_x, tx = tile - ty * a.tiles_x;
+          const uint32_t x = tx * a.tile_w + (l & (a.tile_w - 1u)), y = ty * (32u / a.tile_w) + l / a.tile_w;
+          if (x < (uint32_t)a.img_width && y * (uint32_t)a.img_width + x < (uint32_t)a.pixel_count) {
+            pix = (int)(y * (uint32_t)a.img_width + x);
+            waiting = true;
+          }
         } else {
           exhausted = true;
         }

@@ -219,6 +219,57 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
   const V3 inv = v3(fminf(fmaxf(frcp(r.d.x), -big), big), fminf(fmaxf(frcp(r.d.y), -big), big), fminf(fmaxf(frcp(r.d.z), -big), big));
   const V3 noi = v3(-(r.o.x * inv.x), -(r.o.y * inv.y), -(r.o.z * inv.z));
   const float slack = fminf((fabsf(noi.x) + fabsf(noi.y) + fabsf(noi.z)) * 4.76837158e-7f, 3.0e38f);
+#ifdef RT_WHILE_WHILE
+  // while-while: walk inner nodes until this lane holds a leaf (lanes re-converge behind the inner loop, so the
+  // primitive tests of a warp run together), test it, pop, repeat
+  int sp = 0;
+  uint32_t cur = sc.fast_root;
+  for (;;) {
+    while (rtd::ref_kind(cur) == rtd::K_BVH) {
+      const uint32_t idx = rtd::ref_index(cur);
+      const float4 n0 = ldg4(sc.fast_nodes + 4 * idx);
+      const float4 n1 = ldg4(sc.fast_nodes + 4 * idx + 1);
+      const float4 n2 = ldg4(sc.fast_nodes + 4 * idx + 2);
+      const float4 n3 = ldg4(sc.fast_nodes + 4 * idx + 3);
+      cnt.box(2);
+      const float c0x0 = fmaf(n0.x, inv.x, noi.x), c0x1 = fmaf(n0.y, inv.x, noi.x);
+      const float c0y0 = fmaf(n0.z, inv.y, noi.y), c0y1 = fmaf(n0.w, inv.y, noi.y);
+      const float c0z0 = fmaf(n2.x, inv.z, noi.z), c0z1 = fmaf(n2.y, inv.z, noi.z);
+      const float c1x0 = fmaf(n1.x, inv.x, noi.x), c1x1 = fmaf(n1.y, inv.x, noi.x);
+      const float c1y0 = fmaf(n1.z, inv.y, noi.y), c1y1 = fmaf(n1.w, inv.y, noi.y);
+      const float c1z0 = fmaf(n2.z, inv.z, noi.z), c1z1 = fmaf(n2.w, inv.z, noi.z);
+      const float e0 = fmaxf(fmaxf(fminf(c0x0, c0x1), fminf(c0y0, c0y1)), fmaxf(fminf(c0z0, c0z1), tmin));
+      float x0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), tmax));
+      const float e1 = fmaxf(fmaxf(fminf(c1x0, c1x1), fminf(c1y0, c1y1)), fmaxf(fminf(c1z0, c1z1), tmin));
+      float x1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), tmax));
+      x0 = fmaf(x0, 1.000001f, slack); x1 = fmaf(x1, 1.000001f, slack);
+      const bool h0 = e0 <= x0, h1 = e1 <= x1;
+      const uint32_t r0 = __float_as_uint(n3.x), r1 = __float_as_uint(n3.y);
+      if (h0 && h1) {
+        const bool swap = e1 < e0;
+        cur = swap ? r1 : r0;
+        stk[(sp++) * stride] = swap ? r0 : r1;
+      } else if (h0 || h1) {
+        cur = h0 ? r0 : r1;
+      } else if (sp > 0) {
+        cur = stk[(--sp) * stride];
+      } else {
+        cur = 0xffffffffu;                                // nothing left: K_NONE with every index bit set
+      }
+    }
+    if (cur == 0xffffffffu) break;
+    const uint32_t kind = rtd::ref_kind(cur), idx = rtd::ref_index(cur);
+    if (kind == rtd::K_SPHERE) {
+      cnt.sphere();
+      result |= hit_sphere(sc, idx, r, a, tmin, tmax, h);
+    } else if (kind == rtd::K_QUAD || kind == rtd::K_TRIANGLE) {
+      cnt.planar();
+      result |= hit_planar(sc, idx, kind == rtd::K_TRIANGLE, r, tmin, tmax, h);
+    }                                                     // K_NONE index 0: the empty second child of a one-primitive scene
+    if (sp == 0) break;
+    cur = stk[(--sp) * stride];
+  }
+#else
   int sp = 0;
   uint32_t cur = sc.fast_root;
   for (;;) {
@@ -263,6 +314,7 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
     if (sp == 0) break;
     cur = stk[(--sp) * stride];
   }
+#endif
   return result;
 }
 

@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Sweep the chunk size (env RT_CHUNK, 0 = automatic) on BASELINE configs; RT_B200_LIB selects a library variant
-(tools/build_variants.sh).  usage: gpu_sweep.py CONFIG[:spp] ... -- chunk[,claim_group] ...
+(tools/build_variants.sh).  usage: gpu_sweep.py CONFIG[:spp] ... -- chunk[,claim_group[,tile_w]] ...   (0 = automatic)
 Prints one JSON line per run; the image must not depend on the knobs."""
 import hashlib
 import json
@@ -26,9 +26,10 @@ def main():
             spp = int(spp_s)
         first = None
         for k in knobs:
-            ch, _, grp = k.partition(",")
+            ch, grp, tw = (k.split(",") + ["0", "8"])[:3] if "," in k else (k, "0", "8")
             os.environ["RT_CHUNK"] = ch
-            os.environ["RT_CLAIM_GROUP"] = grp or "1"
+            os.environ["RT_CLAIM_GROUP"] = grp
+            os.environ["RT_TILE_W"] = tw
             ctx = rt.Context(0)
             hs = rt.HostScene(scene)
             ctx.upload(hs, trav)
@@ -39,7 +40,7 @@ def main():
                 ms.append(st.render_ms)
             digest = hashlib.sha1(img.tobytes()).hexdigest()[:12]
             first = first or digest
-            print(json.dumps(dict(config=name, spp=spp, chunk=int(ch), group=int(grp or 1), lib=os.path.basename(os.environ.get("RT_B200_LIB", "default")), ms=round(min(ms), 3),
+            print(json.dumps(dict(config=name, spp=spp, chunk=int(ch), group=int(grp), tile_w=int(tw), lib=os.path.basename(os.environ.get("RT_B200_LIB", "default")), ms=round(min(ms), 3),
                                   mpaths_s=round(st.paths / min(ms) / 1e3, 1), mrays_s=round(st.rays / min(ms) / 1e3, 1),
                                   same_image=digest == first, regs=st.regs_per_thread, bps=st.blocks_per_sm)), flush=True)
             hs.close()
