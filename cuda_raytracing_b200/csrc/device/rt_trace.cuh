@@ -41,8 +41,10 @@ struct OpCount {
 };
 
 // ---- sphere (rt.cu:1093-1123): a = d.d is passed in (it only changes when a wrapper rotates the ray) ----
-__device__ __forceinline__ bool hit_sphere(const Scene &sc, uint32_t idx, const Ray &r, float a, float tmin, float &tmax,
-                                           Hit &h) {
+// The test (which root, if any, lies in (tmin,tmax)) and the hit record are separate so that the warp-scheduled
+// kernel can carry only (t, prim) through a traversal and build the record once, for the closest hit.
+__device__ __forceinline__ bool sphere_root(const Scene &sc, uint32_t idx, const Ray &r, float a, float tmin, float tmax,
+                                            float &root_out) {
   const float4 s0 = ldg4(sc.spheres + 2 * idx);
   const float4 s1 = ldg4(sc.spheres + 2 * idx + 1);
   const V3 c = v3(ffma(r.time, s1.x, s0.x), ffma(r.time, s1.y, s0.y), ffma(r.time, s1.z, s0.z));   // movement_path_at
@@ -56,6 +58,13 @@ __device__ __forceinline__ bool hit_sphere(const Scene &sc, uint32_t idx, const 
   float root = fdiv(fsub(-b, sq), a2);
   if (tmin >= root || root >= tmax) root = fdiv(fsub(sq, b), a2);
   if (!(tmin < root && root < tmax)) return false;
+  root_out = root;
+  return true;
+}
+__device__ __forceinline__ void sphere_record(const Scene &sc, uint32_t idx, const Ray &r, float root, Hit &h) {
+  const float4 s0 = ldg4(sc.spheres + 2 * idx);
+  const float4 s1 = ldg4(sc.spheres + 2 * idx + 1);
+  const V3 c = v3(ffma(r.time, s1.x, s0.x), ffma(r.time, s1.y, s0.y), ffma(r.time, s1.z, s0.z));
   h.t = root;
   h.p = along(r.o, root, r.d);
   const float inv_r = frcp(s0.w);
@@ -71,13 +80,33 @@ __device__ __forceinline__ bool hit_sphere(const Scene &sc, uint32_t idx, const 
   h.front = dot_yfirst(r.d, n) < 0.0f;                     // hit_record_set_face_normal (rt.cu:983-987)
   h.n = h.front ? n : vneg(n);
   h.prim = idx;
+}
+__device__ __forceinline__ bool hit_sphere(const Scene &sc, uint32_t idx, const Ray &r, float a, float tmin, float &tmax,
+                                           Hit &h) {
+  float root;
+  if (!sphere_root(sc, idx, r, a, tmin, tmax, root)) return false;
+  sphere_record(sc, idx, r, root, h);
   tmax = root;
   return true;
 }
 
 // ---- quad / triangle (rt.cu:1131-1175 with geom_calc_hit 1060-1077) ----
-__device__ __forceinline__ bool hit_planar(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float tmin, float &tmax,
-                                           Hit &h) {
+__device__ __forceinline__ bool planar_inside(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float t, V3 &p,
+                                              float &alpha, float &beta) {
+  const float4 p1 = ldg4(sc.planars + 4 * idx + 1);        // q, w.x
+  const float4 p2 = ldg4(sc.planars + 4 * idx + 2);        // v, w.y
+  const float4 p3 = ldg4(sc.planars + 4 * idx + 3);        // u, w.z
+  p = along(r.o, t, r.d);
+  const V3 pl = vsub(p, v3(p1.x, p1.y, p1.z));
+  const V3 w = v3(p1.w, p2.w, p3.w);
+  alpha = dot_yfirst(w, cross(pl, v3(p2.x, p2.y, p2.z)));
+  beta = dot_yfirst(w, cross(v3(p3.x, p3.y, p3.z), pl));
+  bool inside = (0.0f <= alpha && alpha <= 1.0f) && (0.0f <= beta && beta <= 1.0f);
+  if (triangle) inside = inside && (fadd(alpha, beta) <= 1.0f);
+  return inside;
+}
+__device__ __forceinline__ bool planar_t(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float tmin, float tmax,
+                                         float &t_out) {
   const float4 p0 = ldg4(sc.planars + 4 * idx);            // normal, d
   const V3 n = v3(p0.x, p0.y, p0.z);
   const float denom = dot_yfirst(n, r.d);
@@ -85,21 +114,27 @@ __device__ __forceinline__ bool hit_planar(const Scene &sc, uint32_t idx, bool t
   if (!(fabsf(denom) > 1e-8f)) return false;
   const float t = fdiv(fsub(p0.w, dot_yfirst(n, r.o)), denom);
   if (!(tmin <= t && t <= tmax)) return false;
-  const float4 p1 = ldg4(sc.planars + 4 * idx + 1);        // q, w.x
-  const float4 p2 = ldg4(sc.planars + 4 * idx + 2);        // v, w.y
-  const float4 p3 = ldg4(sc.planars + 4 * idx + 3);        // u, w.z
-  const V3 p = along(r.o, t, r.d);
-  const V3 pl = vsub(p, v3(p1.x, p1.y, p1.z));
-  const V3 w = v3(p1.w, p2.w, p3.w);
-  const float alpha = dot_yfirst(w, cross(pl, v3(p2.x, p2.y, p2.z)));
-  const float beta = dot_yfirst(w, cross(v3(p3.x, p3.y, p3.z), pl));
-  bool inside = (0.0f <= alpha && alpha <= 1.0f) && (0.0f <= beta && beta <= 1.0f);
-  if (triangle) inside = inside && (fadd(alpha, beta) <= 1.0f);
-  if (!inside) return false;
-  h.u = alpha; h.v = beta; h.t = t; h.p = p;
+  V3 p; float alpha, beta;
+  if (!planar_inside(sc, idx, triangle, r, t, p, alpha, beta)) return false;
+  t_out = t;
+  return true;
+}
+__device__ __forceinline__ void planar_record(const Scene &sc, uint32_t idx, const Ray &r, float t, Hit &h) {
+  const float4 p0 = ldg4(sc.planars + 4 * idx);
+  const V3 n = v3(p0.x, p0.y, p0.z);
+  const float denom = dot_yfirst(n, r.d);
+  float alpha, beta;
+  planar_inside(sc, idx, false, r, t, h.p, alpha, beta);
+  h.u = alpha; h.v = beta; h.t = t;
   h.front = denom < 0.0f;
   h.n = h.front ? n : vneg(n);
   h.prim = sc.sphere_count + idx;
+}
+__device__ __forceinline__ bool hit_planar(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float tmin, float &tmax,
+                                           Hit &h) {
+  float t;
+  if (!planar_t(sc, idx, triangle, r, tmin, tmax, t)) return false;
+  planar_record(sc, idx, r, t, h);
   tmax = t;
   return true;
 }
@@ -209,7 +244,9 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
 template <class C>
 __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float tmin, float tmax, Hit &h,
                                            uint32_t *stk, const int stride, C &cnt) {
-  bool result = false;
+  // only (tmax, primitive) are carried through the walk; the hit record is built once, for the closest hit, with
+  // the same formulas hit_sphere / hit_planar use (identical bits)
+  uint32_t best = 0xffffffffu;
   const float a = dot_xfirst(r.d, r.d);
   // slab planes as one fma each: t = plane * inv - o * inv.  The rounding of o * inv moves a plane by up to
   // |o * inv| * 2^-24 in t, so the overlap test gets 8x that much slack (and a relative one for the fma itself):
@@ -261,10 +298,12 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
     const uint32_t kind = rtd::ref_kind(cur), idx = rtd::ref_index(cur);
     if (kind == rtd::K_SPHERE) {
       cnt.sphere();
-      result |= hit_sphere(sc, idx, r, a, tmin, tmax, h);
+      float root;
+      if (sphere_root(sc, idx, r, a, tmin, tmax, root)) { tmax = root; best = cur; }
     } else if (kind == rtd::K_QUAD || kind == rtd::K_TRIANGLE) {
       cnt.planar();
-      result |= hit_planar(sc, idx, kind == rtd::K_TRIANGLE, r, tmin, tmax, h);
+      float tt;
+      if (planar_t(sc, idx, kind == rtd::K_TRIANGLE, r, tmin, tmax, tt)) { tmax = tt; best = cur; }
     }                                                     // K_NONE index 0: the empty second child of a one-primitive scene
     if (sp == 0) break;
     cur = stk[(--sp) * stride];
@@ -306,16 +345,21 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
       }
     } else if (kind == rtd::K_SPHERE) {
       cnt.sphere();
-      result |= hit_sphere(sc, idx, r, a, tmin, tmax, h);
+      float root;
+      if (sphere_root(sc, idx, r, a, tmin, tmax, root)) { tmax = root; best = cur; }
     } else if (kind == rtd::K_QUAD || kind == rtd::K_TRIANGLE) {
       cnt.planar();
-      result |= hit_planar(sc, idx, kind == rtd::K_TRIANGLE, r, tmin, tmax, h);
+      float tt;
+      if (planar_t(sc, idx, kind == rtd::K_TRIANGLE, r, tmin, tmax, tt)) { tmax = tt; best = cur; }
     }                                                     // K_NONE: the empty second child of a one-primitive scene
     if (sp == 0) break;
     cur = stk[(--sp) * stride];
   }
 #endif
-  return result;
+  if (best == 0xffffffffu) return false;
+  if (rtd::ref_kind(best) == rtd::K_SPHERE) sphere_record(sc, rtd::ref_index(best), r, tmax, h);
+  else planar_record(sc, rtd::ref_index(best), r, tmax, h);
+  return true;
 }
 
 }  // namespace rtt

@@ -255,3 +255,63 @@ def test_cli_writes_reference_ppm(product_lib, oracle):
             d2 = os.path.join(d, "ref"); os.mkdir(d2)
             subprocess.run([os.path.join(common.ROOT, "oracle", "_ref", "raytracing_ref"), "13", "s2", "b4"], cwd=d2, capture_output=True, timeout=600, check=True)
             assert open(os.path.join(d2, "mblur.ppm"), "rb").read() == data      # byte-identical file
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sid,floor_db", [(0, 40.0), (1, 30.0)])
+def test_tier2_converged_images_vs_reference_gpu(gpu_ctx, oracle, product_lib, sid, floor_db):
+    """Tier 2 (north_star): at 4096 spp the statistical modes -- flattened instances (RT_TRAVERSAL_FAST) and sample
+    sharding (2 virtual ranks x 2048 spp, disjoint XORWOW subsequences, summed) -- match the reference's own GPU render.
+    PSNR on the 8-bit images, tolerance: >= 40 dB on the sky-lit scene; the Cornell box (small light, black background)
+    is noise-limited at 4096 spp, two independent estimates of it differ by more than that, so its floor is lower."""
+    if not os.path.exists(REF_EXT):
+        pytest.skip("reference binary not built")
+    hs = product_lib.HostScene(sid)
+    width, spp, b = 128, 4096, 50
+    p = hs.params(width, spp, b)
+    ref8 = oracle.resolve_rgb8(_ref_gpu_image(sid, width, spp, b, p.img_height))
+    gpu_ctx.upload(hs, product_lib.RT_TRAVERSAL_FAST)
+    _, fast8, st = gpu_ctx.render(p)
+    assert st.traversal_used == product_lib.RT_TRAVERSAL_FAST
+    db_fast = common.psnr8(fast8, ref8)
+    n = p.img_width * p.img_height
+    total = np.zeros((p.img_height, p.img_width, 3), np.float32)
+    for g in range(2):                                                   # the reduce of bench.py / render.py, done on the host
+        q = hs.params(width, spp // 2, b, subsequence_offset=g * n, flags=product_lib.RT_RENDER_OUTPUT_SUM)
+        part, _, _ = gpu_ctx.render(q)
+        total += part
+    shard8 = oracle.resolve_rgb8(total * np.float32(1.0 / spp))
+    db_shard = common.psnr8(shard8, ref8)
+    print("tier2 scene %d: PSNR fast %.2f dB, sample-sharded %.2f dB" % (sid, db_fast, db_shard))
+    assert db_fast >= floor_db and db_shard >= floor_db, (sid, db_fast, db_shard)
+    hs.close()
+
+
+@pytest.mark.gpu
+def test_image_does_not_depend_on_scheduling_knobs(product_lib):
+    """Chunk size, tile shape and claim grouping only change WHO renders a pixel's samples and when, never the
+    samples: the image is bit-identical whatever the knobs (contexts read them from the environment at creation)."""
+    hs = product_lib.HostScene(2)
+    p = hs.params(200, 24, 12)
+    images = []
+    knobs = [{}, {"RT_CHUNK": "5"}, {"RT_CHUNK": "1000000"}, {"RT_CHUNK": "7", "RT_TILE_W": "32", "RT_CLAIM_GROUP": "1"},
+             {"RT_CHUNK": "3", "RT_TILE_W": "4", "RT_CLAIM_GROUP": "32"}]
+    saved = {k: os.environ.get(k) for k in ("RT_CHUNK", "RT_TILE_W", "RT_CLAIM_GROUP")}
+    try:
+        for kn in knobs:
+            for k in saved:
+                os.environ.pop(k, None)
+            os.environ.update(kn)
+            ctx = product_lib.Context(0)
+            ctx.upload(hs, product_lib.RT_TRAVERSAL_AUTO)
+            img, _, _ = ctx.render(p)
+            images.append(img)
+            ctx.close()
+    finally:
+        for k, v in saved.items():
+            os.environ.pop(k, None)
+            if v is not None:
+                os.environ[k] = v
+    for img in images[1:]:
+        assert np.array_equal(common.bits(img), common.bits(images[0]))
+    hs.close()
