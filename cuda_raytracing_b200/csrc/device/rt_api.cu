@@ -240,7 +240,8 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
     a.chunk_samples = chunk;
     a.chunk_count = (spp + chunk - 1) / chunk;
     const uint32_t tw = (uint32_t)ctx->tile_w, th = 32u / tw, rows = (uint32_t)(row1 - row0);
-    a.tile_w = tw;
+    a.tile_shift = 0; while ((1u << a.tile_shift) < tw) ++a.tile_shift;
+    a.first_row = row0;
     a.tiles_x = ((uint32_t)p->img_width + tw - 1) / tw;
     a.slots_per_chunk = a.tiles_x * ((rows + th - 1) / th) * 32u;
     a.item_count = (unsigned long long)a.slots_per_chunk * (unsigned long long)a.chunk_count;

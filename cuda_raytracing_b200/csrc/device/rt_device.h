@@ -81,7 +81,8 @@ struct RenderArgs {
   unsigned long long *counters; // [0] next work item, [1] rays traced, [2..13] operation counters (count_ops)
   unsigned long long item_count;// slots_per_chunk * chunk_count work items; item = chunk * slots_per_chunk + slot
   uint32_t slots_per_chunk;     // 32 * number of 32-pixel tiles covering the rendered rows (>= pixel_count)
-  uint32_t tiles_x, tile_w;     // tiles per row of tiles; tile width in pixels (power of two <= 32, height = 32 / width)
+  uint32_t tiles_x, tile_shift; // tiles per row of tiles; log2 of the tile width (tile = 2^s x 2^(5-s) pixels)
+  int32_t first_row;            // first_pixel / img_width
   int32_t chunk_samples, chunk_count;   // a pixel's samples are produced in order, chunk_samples at a time
   int32_t claim_group;          // idle lanes of a warp claim work items together, this many at a time
   int32_t img_width, img_height, samples_per_pixel, max_bounces;

@@ -71,8 +71,10 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
   uint32_t *stk = smem + threadIdx.x;
   const int stride = blockDim.x;
   PerlinSmem *perlin = nullptr;
+  float *coop = nullptr;                                // per-warp scratch of the cooperative turbulence
   if (sc.perlin_tables > 0) {
     perlin = reinterpret_cast<PerlinSmem *>(smem + rtd::STACK_CAPACITY * blockDim.x);
+    coop = reinterpret_cast<float *>(perlin + 1) + (threadIdx.x >> 5) * rts::COOP_WORDS_PER_WARP;
     stage_perlin(sc, perlin);
     __syncthreads();
   }
@@ -116,14 +118,23 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
         if (item < a.item_count) {
           // items walk the range in tiles of 32 pixels (tile_w x 32/tile_w): a warp that claims together gets a compact
           // block of the image, whose rays visit the same nodes.  Slots of a border tile that fall outside are no-ops.
-          chunk = (int)(item / (unsigned long long)a.slots_per_chunk);
-          const uint32_t slot = (uint32_t)(item - (unsigned long long)chunk * (unsigned long long)a.slots_per_chunk);
+          uint32_t slot;
+          if (a.item_count <= 0xffffffffull) {                // the usual case: 32-bit divide
+            chunk = (int)((uint32_t)item / a.slots_per_chunk);
+            slot = (uint32_t)item - (uint32_t)chunk * a.slots_per_chunk;
+          } else {
+            chunk = (int)(item / (unsigned long long)a.slots_per_chunk);
+            slot = (uint32_t)(item - (unsigned long long)chunk * (unsigned long long)a.slots_per_chunk);
+          }
           const uint32_t tile = slot >> 5, l = slot & 31u;
           const uint32_t ty = tile / a.tiles_x, tx = tile - ty * a.tiles_x;
-          const uint32_t x = tx * a.tile_w + (l & (a.tile_w - 1u)), y = ty * (32u / a.tile_w) + l / a.tile_w;
+          const uint32_t x = (tx << a.tile_shift) + (l & ((1u << a.tile_shift) - 1u)), y = (ty << (5u - a.tile_shift)) + (l >> a.tile_shift);
           if (x < (uint32_t)a.img_width && y * (uint32_t)a.img_width + x < (uint32_t)a.pixel_count) {
             pix = (int)(y * (uint32_t)a.img_width + x);
             waiting = true;
+            const float fi = (float)(a.first_row + (int)y), fj = (float)x;     // rt.cu:1561-1567
+            base = v3(fadd(ffma(fj, du.x, fmul(fi, dv.x)), a.p00[0]), fadd(ffma(fj, du.y, fmul(fi, dv.y)), a.p00[1]),
+                      fadd(ffma(fj, du.z, fmul(fi, dv.z)), a.p00[2]));
           }
         } else {
           exhausted = true;
@@ -140,10 +151,6 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
       const int gp = a.first_pixel + pix;
       float *out = a.pixels + 3 * (size_t)gp;
       acc = chunk ? v3(__ldcg(out), __ldcg(out + 1), __ldcg(out + 2)) : v3(0.0f, 0.0f, 0.0f);
-      const int j = gp % a.img_width, i = (gp - j) / a.img_width;     // rt.cu:1561-1567
-      const float fi = (float)i, fj = (float)j;
-      base = v3(fadd(ffma(fj, du.x, fmul(fi, dv.x)), a.p00[0]), fadd(ffma(fj, du.y, fmul(fi, dv.y)), a.p00[1]),
-                fadd(ffma(fj, du.z, fmul(fi, dv.z)), a.p00[2]));
       const int done = chunk * a.chunk_samples;
       samples_left = a.samples_per_pixel - done < a.chunk_samples ? a.samples_per_pixel - done : a.chunk_samples;
       new_path = true;
@@ -153,10 +160,10 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
       }
     }
     if (!__any_sync(full, pix >= 0)) break;
-    if (pix < 0 || waiting) continue;
+    const bool live = pix >= 0 && !waiting;               // lanes without work stay in step (the warp shares work below)
 
     // ---- (1) camera ray generation (rt.cu:1570-1578) ----
-    if (new_path) {
+    if (live && new_path) {
       new_path = false;
       V3 o = cam;
       if (!(a.defocus_angle <= 0.0f)) {
@@ -175,8 +182,10 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
 
     // ---- (2) one bounce: closest hit, (3) emission + scatter ----
     V3 result = v3(0.0f, 0.0f, 0.0f);
-    bool done = (budget <= 0);
-    if (!done) {
+    bool done = live && (budget <= 0);
+    bool noise_pending = false;                           // this bounce's attenuation is a Perlin texture, evaluated below
+    V3 noise_p = cam; float noise_scale = 0.0f;
+    if (live && !done) {
       ++rays;
       Hit h; h.u = 0.0f; h.v = 0.0f; h.t = 0.0f; h.prim = 0; h.front = 0; h.p = cam; h.n = cam;
       if (trace<MODE>(sc, ray, h, stk, stride, cnt)) {
@@ -190,7 +199,8 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
         const V3 U = rng_unit_vector(rng);               // rt.cu:500-501: drawn for EVERY hit, whatever the material
         const float rtest = rng_uniform(rng);
         V3 dout, att;
-        if (rts::scatter(sc, m0, m1, ray.d, h, U, rtest, perlin, dout, att)) {
+        if (rts::scatter(sc, m0, m1, ray.d, h, U, rtest, perlin, dout, att, &noise_pending)) {
+          noise_p = h.p; noise_scale = m1.w;
           ray.o = h.p; ray.d = dout;
           if (depth != capacity) { att_r[depth] = att.x; att_g[depth] = att.y; att_b[depth] = att.z; ++depth; }
           --budget;
@@ -202,6 +212,18 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
       } else {
         result = bg;
         done = true;
+      }
+    }
+
+    // ---- (3b) Perlin textures of this bounce, all lanes of the warp working for the lanes that need one ----
+    if (perlin != nullptr) {                              // block-uniform
+      const unsigned mn = __ballot_sync(full, noise_pending);
+      if (mn) {
+        const float turb = rts::coop_turbulence7(perlin, coop, mn, noise_pending, noise_p);
+        if (noise_pending) {                              // the slot scatter pushed (depth - 1) gets the colour
+          const V3 c = rts::noise_colour(turb, noise_scale, noise_p.z);
+          att_r[depth - 1] = c.x; att_g[depth - 1] = c.y; att_b[depth - 1] = c.z;
+        }
       }
     }
 
@@ -439,7 +461,7 @@ cudaError_t launch_probe_texture(const rtd::Scene &scene, uint64_t n, uint32_t t
 template <int MODE, int MAXB, bool COUNT>
 static cudaError_t launch_render_t(const RenderArgs &args, int sm_count, cudaStream_t stream, LaunchInfo *info) {
   size_t smem = sizeof(uint32_t) * rtd::STACK_CAPACITY * RT_BLOCK;
-  if (args.scene.perlin_tables > 0) smem += sizeof(PerlinSmem);
+  if (args.scene.perlin_tables > 0) smem += sizeof(PerlinSmem) + sizeof(float) * rts::COOP_WORDS_PER_WARP * (RT_BLOCK / 32);
   auto kernel = render_kernel<MODE, MAXB, COUNT>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;

@@ -77,6 +77,36 @@ __device__ __forceinline__ float perlin_turbulence7(const T &tab, V3 p) {
   }
   return fabsf(accum);
 }
+// ---- warp-cooperative turbulence ----------------------------------------------------------------------------------
+// The 7 octaves of perlin_turbulence are independent noise values at p, 2p, 4p, ... (exact doublings) that only
+// meet in the final accumulate chain.  In a warp only the lanes that hit a noise-textured surface need one, so the
+// (requests x 7) octave evaluations are dealt round-robin to ALL 32 lanes and each requester then runs the
+// reference's accumulate chain over its 7 values: same bits, 32 lanes busy instead of the few that hit.
+// scratch: 3 * 32 floats of points + 7 * 32 floats of octave values per warp.
+constexpr int COOP_WORDS_PER_WARP = 3 * 32 + 7 * 32;
+__device__ __forceinline__ float coop_turbulence7(const PerlinSmem *table, float *scratch, unsigned requesters, bool mine, V3 p) {
+  const unsigned lane = threadIdx.x & 31u;
+  float *pts = scratch, *vals = scratch + 3 * 32;
+  const int rank = __popc(requesters & ((1u << lane) - 1u));
+  if (mine) { pts[3 * rank] = p.x; pts[3 * rank + 1] = p.y; pts[3 * rank + 2] = p.z; }
+  __syncwarp();
+  const int tasks = __popc(requesters) * 7;
+  PerlinShared tab; tab.t = table;
+  for (int t = (int)lane; t < tasks; t += 32) {
+    const int req = t / 7, oct = t - req * 7;
+    const float s = (float)(1 << oct);                                        // p * 2^oct == oct doublings, exactly
+    vals[t] = perlin_noise(tab, v3(fmul(pts[3 * req], s), fmul(pts[3 * req + 1], s), fmul(pts[3 * req + 2], s)));
+  }
+  __syncwarp();
+  float accum = 0.0f, weight = 1.0f;
+  if (mine) {
+#pragma unroll
+    for (int o = 0; o < 7; ++o) { accum = ffma(weight, vals[7 * rank + o], accum); weight = fmul(weight, 0.5f); }
+  }
+  __syncwarp();                                                               // scratch is reused by the next call
+  return fabsf(accum);
+}
+
 // noise texture colour (rt.cu:386-395): 0.5*(1 + sin(scale*z + 10*turb))
 __device__ __forceinline__ V3 noise_colour(float turb, float scale, float z) {
   const float c = fmul(fadd(sinf(ffma(z, scale, fmul(turb, 10.0f))), 1.0f), 0.5f);
@@ -146,8 +176,11 @@ __device__ __forceinline__ V3 unit_or_zero(V3 a, float len) {                 //
 
 // material_scatter_common (rt.cu:452-490).  `U` and `rtest` are drawn by the caller for EVERY hit, whatever the
 // material (rt.cu:500-501, Q5).  Returns false when the path ends here (absorbed metal bounce, or a light).
+// `defer_noise` (optional): a lambertian whose texture is the shared-memory Perlin table does not evaluate it here but
+// sets the flag; the render kernel then evaluates the pending textures of the whole warp cooperatively.
 __device__ __forceinline__ bool scatter(const Scene &sc, const uint4 m0, const float4 m1, const V3 din, const rtt::Hit &h,
-                                        const V3 U, const float rtest, const PerlinSmem *smem_perlin, V3 &dout, V3 &att) {
+                                        const V3 U, const float rtest, const PerlinSmem *smem_perlin, V3 &dout, V3 &att,
+                                        bool *defer_noise = nullptr) {
   const V3 n = h.n;
   const uint32_t type = m0.x & 0xffu;
   if (type == rtd::M_LAMBERTIAN) {
@@ -155,7 +188,8 @@ __device__ __forceinline__ bool scatter(const Scene &sc, const uint4 m0, const f
     const float tiny = 1e-8f;                                                 // vec3_is_near_zero (vec3.h:177-181)
     if (fabsf(d.x) < tiny && fabsf(d.y) < tiny && fabsf(d.z) < tiny) d = n;
     dout = d;
-    att = material_texture(sc, m0, m1, h, smem_perlin);
+    if (defer_noise && smem_perlin && ((m0.x >> 8) & 0xffu) == rtd::TK_NOISE && m0.z == 0) { *defer_noise = true; att = v3(0.0f, 0.0f, 0.0f); }
+    else att = material_texture(sc, m0, m1, h, smem_perlin);
     return true;
   }
   if (type == rtd::M_METAL) {
