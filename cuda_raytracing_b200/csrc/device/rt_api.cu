@@ -62,6 +62,7 @@ struct rt_context {
   DeviceBuffer b_rng_mats, b_rng_init, b_rng_states, b_progress, b_counters;   // b_rng_init: pristine states (cache)
   int chunk_samples = 0;                                   // 0 = automatic; env RT_CHUNK overrides (tuning knob)
   int claim_group = 0;                                     // 0 = automatic; env RT_CLAIM_GROUP (tuning knob)
+  uint32_t treelet_min = 8;                                // env RT_TREELET_MIN: smallest wrapper-free subtree given an own BVH (0 = none)
   int tile_w = 8;                                          // work items walk 8x4-pixel tiles; env RT_TILE_W (1..32, power of 2)
   uint64_t rng_seed = 0, rng_first = 0, rng_count = 0; bool rng_valid = false;
   // scratch for rt_render (host-buffer path)
@@ -104,6 +105,7 @@ int rt_context_create(int device_id, rt_context **out) {
   for (int i = 0; i < 4; ++i) cudaEventCreate(&ctx->ev[i]);
   if (const char *v = getenv("RT_CHUNK")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 24)) ctx->chunk_samples = (int)x; }
   if (const char *v = getenv("RT_TILE_W")) { const long x = strtol(v, nullptr, 10); if (x >= 1 && x <= 32 && (x & (x - 1)) == 0) ctx->tile_w = (int)x; }
+  if (const char *v = getenv("RT_TREELET_MIN")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 30)) ctx->treelet_min = (uint32_t)x; }
   if (const char *v = getenv("RT_CLAIM_GROUP")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= 32) ctx->claim_group = (int)x; }
   std::vector<uint32_t> mats;
   rtp::xorwow_sequence_matrices(mats);
@@ -155,7 +157,7 @@ int rt_scene_upload(rt_context *ctx, const rt_scene_desc *desc, uint32_t travers
   ctx->has_scene = false;
   ctx->packed = rtp::PackedScene();
   rtp::PackedScene &p = ctx->packed;
-  int rc = rtp::pack_scene(*desc, traversal, p);
+  int rc = rtp::pack_scene(*desc, traversal, p, ctx->treelet_min);
   if (rc != RT_OK) return fail(ctx, rc, p.error);
   cudaStream_t s = ctx->stream;
 #define UP(buf, vec) RT_CUDA(ctx, ctx->buf.upload((vec).data(), (vec).size() * sizeof((vec)[0]), s))
@@ -261,7 +263,8 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   a.sample_scale = (p->flags & RT_RENDER_OUTPUT_SUM) ? 1.0f : 1.0f / (float)p->samples_per_pixel;   // rt.cu:1657
   a.count_rays = (p->flags & (RT_RENDER_COUNT_RAYS | RT_RENDER_COUNT_OPS)) ? 1u : 0u;
   a.count_ops = (p->flags & RT_RENDER_COUNT_OPS) ? 1u : 0u;
-  const int mode = ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? 1 : 0;
+  // kernel variant: 1 = own BVH over the whole scene, 2 = reference order with treelets, 0 = reference order
+  const int mode = ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? 1 : (ctx->packed.treelets > 0 ? 2 : 0);
   RT_CUDA(ctx, rtk::launch_render(a, mode, ctx->sm_count, s, &ctx->last_launch));
   ++launches;
   if (stats) {

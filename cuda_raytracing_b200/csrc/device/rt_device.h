@@ -35,6 +35,10 @@ constexpr uint32_t INDEX_MASK = (1u << KIND_SHIFT) - 1u;
 RTD_HD uint32_t make_ref(uint32_t kind, uint32_t index) { return (kind << KIND_SHIFT) | index; }
 RTD_HD uint32_t ref_kind(uint32_t r) { return r >> KIND_SHIFT; }
 RTD_HD uint32_t ref_index(uint32_t r) { return r & INDEX_MASK; }
+// Treelets: inside the reference-order graph a link of kind K_NONE with index i > 0 points at node i - 1 of
+// `fast_nodes` -- an own SAH BVH that stands in for a wrapper-free subtree of the reference's BVH (index 0 stays
+// "nothing": the empty second child of a one-primitive scene).
+RTD_HD uint32_t make_own_ref(uint32_t node) { return (K_NONE << KIND_SHIFT) | (node + 1u); }
 
 // material record: 2 x 16 B per primitive (prim id = sphere index, or sphere_count + planar index) -------
 enum MatType : uint32_t { M_LAMBERTIAN = 0, M_METAL = 1, M_DIELECTRIC = 2, M_DIFFUSE_LIGHT = 3 };   // rt.cu:79-84
@@ -57,6 +61,7 @@ struct Scene {
   // own BVH over world-space primitives (RT_TRAVERSAL_FAST): 4 x float4 per node
   //   n0 = {c0.x0, c0.x1, c0.y0, c0.y1}  n1 = {c1.x0, c1.x1, c1.y0, c1.y1}
   //   n2 = {c0.z0, c0.z1, c1.z0, c1.z1}  n3 = {child0 ref, child1 ref, 0, 0}
+  //   child refs are K_BVH links in the whole-scene BVH, make_own_ref() links in a treelet of the reference graph
   const float4 *fast_nodes;
   uint32_t fast_root;
   // primitives

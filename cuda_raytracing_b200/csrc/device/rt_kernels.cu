@@ -60,7 +60,8 @@ __device__ __forceinline__ void st_volatile_u32(uint32_t *p, uint32_t v) { *rein
 template <int MODE, class C>
 __device__ __forceinline__ bool trace(const Scene &sc, Ray &r, Hit &h, uint32_t *stk, int stride, C &cnt) {
   const float inf = __uint_as_float(0x7f800000u);
-  if (MODE == 0) return rtt::trace_reference(sc, r, 0.001f, inf, h, stk, stride, cnt);
+  if (MODE == 0) return rtt::trace_reference<false>(sc, r, 0.001f, inf, h, stk, stride, cnt);
+  if (MODE == 2) return rtt::trace_reference<true>(sc, r, 0.001f, inf, h, stk, stride, cnt);   // reference order + treelets
   return rtt::trace_fast(sc, r, 0.001f, inf, h, stk, stride, cnt);
 }
 
@@ -386,7 +387,7 @@ __global__ void __launch_bounds__(PROBE_BLOCK) probe_trace_kernel(const Scene sc
   Hit h; h.u = 0.0f; h.v = 0.0f; h.t = 0.0f; h.prim = 0; h.front = 0; h.p = v3(0, 0, 0); h.n = v3(0, 0, 0);
   bool hit;
   rtt::NoCount cnt;
-  if (MODE == 0) hit = rtt::trace_reference(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
+  if (MODE == 0) hit = rtt::trace_reference<true>(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
   else hit = rtt::trace_fast(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
   rt_probe_hit o;
   o.origin[0] = r.o.x; o.origin[1] = r.o.y; o.origin[2] = r.o.z;
@@ -488,9 +489,11 @@ cudaError_t launch_render(const rtd::RenderArgs &args, int mode, int sm_count, c
   const bool small = (args.max_bounces & 255) <= 64;
   if (args.count_ops) {                                  // instrumented build of the same kernel (not the timed one)
     if (mode == 0) return launch_render_t<0, 256, true>(args, sm_count, stream, info);
+    if (mode == 2) return launch_render_t<2, 256, true>(args, sm_count, stream, info);
     return launch_render_t<1, 256, true>(args, sm_count, stream, info);
   }
   if (mode == 0) return small ? launch_render_t<0, 64, false>(args, sm_count, stream, info) : launch_render_t<0, 256, false>(args, sm_count, stream, info);
+  if (mode == 2) return small ? launch_render_t<2, 64, false>(args, sm_count, stream, info) : launch_render_t<2, 256, false>(args, sm_count, stream, info);
   return small ? launch_render_t<1, 64, false>(args, sm_count, stream, info) : launch_render_t<1, 256, false>(args, sm_count, stream, info);
 }
 

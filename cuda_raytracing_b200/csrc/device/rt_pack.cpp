@@ -108,7 +108,8 @@ struct SahBuilder {
   std::vector<Leaf> &leaves;
   std::vector<float4> &nodes;
   uint32_t max_depth = 0;
-  explicit SahBuilder(std::vector<Leaf> &l, std::vector<float4> &n) : leaves(l), nodes(n) {}
+  bool own_links;                                      // treelet: inner links are make_own_ref(), not K_BVH
+  explicit SahBuilder(std::vector<Leaf> &l, std::vector<float4> &n, bool own = false) : leaves(l), nodes(n), own_links(own) {}
 
   // returns the tagged ref of the subtree over leaves[begin,end) and its box
   uint32_t build(size_t begin, size_t end, uint32_t depth, Box &box_out) {
@@ -152,7 +153,7 @@ struct SahBuilder {
     nodes[4 * me + 2] = f4(b0.lo[2], b0.hi[2], b1.lo[2], b1.hi[2]);
     nodes[4 * me + 3] = f4(as_float(r0), as_float(r1), 0.0f, 0.0f);
     box_out = b0; box_grow(box_out, b1);
-    return make_ref(K_BVH, me);
+    return own_links ? make_own_ref(me) : make_ref(K_BVH, me);
   }
 };
 
@@ -165,7 +166,8 @@ struct Packer {
   std::vector<uint32_t> tag;                    // hittable index -> tagged ref (reference graph)
   std::vector<rt_material> sphere_mats, planar_mats;
   std::vector<Leaf> leaves;                     // FAST traversal leaves
-  Packer(const rt_scene_desc &desc, PackedScene &o) : d(desc), out(o) {}
+  uint32_t treelet_min;                         // smallest wrapper-free subtree (primitives) worth an own BVH; 0 = never
+  Packer(const rt_scene_desc &desc, PackedScene &o, uint32_t tmin) : d(desc), out(o), treelet_min(tmin) {}
 
   const rt_hittable &H(uint32_t i) const { return d.hittables[i]; }
 
@@ -189,9 +191,11 @@ struct Packer {
     return idx;
   }
 
-  // exact stack need of the reference-order traversal (see trace_reference): `base` = entries below this one
+  // exact stack need of the reference-order traversal (see trace_reference: every item is pushed, then popped and
+  // worked on): `base` = entries below this subtree's root
   uint32_t stack_need(uint32_t href, uint32_t base, int guard) const {
     if (guard > 64 || href >= d.hittable_count) return base;
+    if (treelet_depth[href] > 0) return base + treelet_depth[href] + 1;    // one pending far child per level + the pair pushed last
     const rt_hittable &h = H(href);
     switch (h.type) {
       case RT_OBJ_BVH_NODE: {
@@ -209,6 +213,81 @@ struct Packer {
       default: return base;
     }
   }
+
+  // ---- treelets: wrapper-free subtrees of the reference BVH get an own SAH BVH (exactness argument in rt_trace.cuh) ----
+  std::vector<int64_t> pure_prims;              // per hittable: primitives below it, or -1 when a wrapper is below it
+  std::vector<uint32_t> treelet_depth;          // per hittable: > 0 on the BVH nodes that were replaced by a treelet
+  int64_t purity(uint32_t href, int guard) {
+    if (guard > 64 || href >= d.hittable_count) return -1;
+    if (pure_prims[href] != -2) return pure_prims[href];
+    const rt_hittable &h = H(href);
+    int64_t n = -1;
+    switch (h.type) {
+      case RT_OBJ_SPHERE: case RT_OBJ_TRIANGLE: case RT_OBJ_QUAD: n = 1; break;
+      case RT_OBJ_STRUCTURE:
+        n = 0;
+        if ((uint64_t)h.u.structure.first + h.u.structure.count > d.hittable_count) { n = -1; break; }
+        for (uint32_t k = 0; k < h.u.structure.count && n >= 0; ++k) {
+          const int64_t c = purity(h.u.structure.first + k, guard + 1);
+          n = c < 0 ? -1 : n + c;
+        }
+        break;
+      case RT_OBJ_BVH_NODE: {
+        if (h.u.bvh.left >= d.world_count || h.u.bvh.right >= d.world_count) break;
+        const int64_t a = purity(d.world_refs[h.u.bvh.left], guard + 1);
+        const int64_t b = h.u.bvh.right == h.u.bvh.left ? 0 : purity(d.world_refs[h.u.bvh.right], guard + 1);
+        n = (a < 0 || b < 0) ? -1 : a + b;
+      } break;
+      default: break;                           // wrappers (and anything unknown) end a pure subtree
+    }
+    pure_prims[href] = n;
+    return n;
+  }
+  void gather(uint32_t href, std::vector<Leaf> &lv, int guard) {
+    if (guard > 64) return;
+    const rt_hittable &h = H(href);
+    switch (h.type) {
+      case RT_OBJ_SPHERE: { Leaf lf; lf.ref = tag[href]; lf.box = box_of(h.u.sphere.bbox); center_leaf(lf); lv.push_back(lf); } break;
+      case RT_OBJ_TRIANGLE: case RT_OBJ_QUAD: { Leaf lf; lf.ref = tag[href]; lf.box = box_of(h.u.planar.bbox); center_leaf(lf); lv.push_back(lf); } break;
+      case RT_OBJ_STRUCTURE: for (uint32_t k = 0; k < h.u.structure.count; ++k) gather(h.u.structure.first + k, lv, guard + 1); break;
+      case RT_OBJ_BVH_NODE:
+        gather(d.world_refs[h.u.bvh.left], lv, guard + 1);
+        if (h.u.bvh.right != h.u.bvh.left) gather(d.world_refs[h.u.bvh.right], lv, guard + 1);
+        break;
+      default: break;
+    }
+  }
+  // top-down over the reference graph: the first BVH node on each path that is wrapper-free and big enough becomes a treelet
+  void plant_treelets(uint32_t href, uint32_t min_prims, int guard) {
+    if (guard > 64 || href >= d.hittable_count) return;
+    const rt_hittable &h = H(href);
+    if (h.type == RT_OBJ_BVH_NODE) {
+      if (treelet_depth[href] > 0) return;
+      const int64_t n = purity(href, 0);
+      if (n >= (int64_t)min_prims && n >= 2) {
+        std::vector<Leaf> lv;
+        gather(href, lv, 0);
+        if (lv.size() >= 2) {
+          SahBuilder sb(lv, out.fast_nodes, true);
+          Box rb;
+          tag[href] = sb.build(0, lv.size(), 0, rb);
+          treelet_depth[href] = sb.max_depth;
+          ++out.treelets; out.treelet_prims += (uint32_t)lv.size();
+          return;
+        }
+      }
+      if (h.u.bvh.left >= d.world_count || h.u.bvh.right >= d.world_count) return;
+      plant_treelets(d.world_refs[h.u.bvh.left], min_prims, guard + 1);
+      if (h.u.bvh.right != h.u.bvh.left) plant_treelets(d.world_refs[h.u.bvh.right], min_prims, guard + 1);
+    } else if (h.type == RT_OBJ_TRANSLATION) {
+      plant_treelets(h.u.translation.child, min_prims, guard + 1);
+    } else if (h.type == RT_OBJ_Y_ROTATION) {
+      plant_treelets(h.u.y_rotation.child, min_prims, guard + 1);
+    } else if (h.type == RT_OBJ_STRUCTURE && (uint64_t)h.u.structure.first + h.u.structure.count <= d.hittable_count) {
+      for (uint32_t k = 0; k < h.u.structure.count; ++k) plant_treelets(h.u.structure.first + k, min_prims, guard + 1);
+    }
+  }
+  static void center_leaf(Leaf &lf) { for (int a = 0; a < 3; ++a) lf.centroid[a] = 0.5f * (lf.box.lo[a] + lf.box.hi[a]); }
 
   // world-space copy of everything below `href` (FAST traversal)
   void flatten(uint32_t href, const Xf &xf, int guard) {
@@ -305,12 +384,18 @@ struct Packer {
         default: out.error = "rt_scene_upload: unknown hittable type"; return RT_ERR_INVALID;
       }
     }
+    // wrapper-free subtrees of the reference BVH -> own SAH treelets (their roots' tags change before links are written)
+    pure_prims.assign(n, -2); treelet_depth.assign(n, 0);
+    const bool want_fast = traversal == RT_TRAVERSAL_FAST || (traversal == RT_TRAVERSAL_AUTO && !out.has_wrappers);
+    if (traversal == RT_TRAVERSAL_AUTO && out.has_wrappers && treelet_min > 0 && d.world_refs[d.root_wref] < n)
+      plant_treelets(d.world_refs[d.root_wref], treelet_min, 0);
     // pass 2: links
     out.ref_nodes.resize(2 * (size_t)n_bvh); out.xforms.resize(n_xf); out.structures.resize(n_st);
     for (uint64_t i = 0; i < n; ++i) {
       const rt_hittable &h = H((uint32_t)i);
       const uint32_t idx = ref_index(tag[i]);
       if (h.type == RT_OBJ_BVH_NODE) {
+        if (treelet_depth[i] > 0) continue;                 // replaced: its links are never followed
         if (h.u.bvh.left >= d.world_count || h.u.bvh.right >= d.world_count) { out.error = "rt_scene_upload: BVH child out of range"; return RT_ERR_INVALID; }
         const rt_aabb &b = h.u.bvh.bbox;
         out.ref_nodes[2 * idx] = f4(b.x0, b.x1, b.y0, b.y1);
@@ -332,8 +417,7 @@ struct Packer {
     out.ref_root = tag[root_href];
     out.ref_stack_need = stack_need(root_href, 0, 0) + 1;
 
-    // own BVH
-    const bool want_fast = traversal == RT_TRAVERSAL_FAST || (traversal == RT_TRAVERSAL_AUTO && !out.has_wrappers);
+    // own BVH over the whole scene
     if (want_fast) {
       Xf id;
       for (uint64_t w = 0; w < d.world_count; ++w) {
@@ -377,9 +461,9 @@ struct Packer {
 
 }  // namespace
 
-int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out) {
+int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out, uint32_t treelet_min) {
   if (traversal > RT_TRAVERSAL_FAST) { out.error = "rt_scene_upload: unknown traversal mode"; return RT_ERR_INVALID; }
-  Packer p(desc, out);
+  Packer p(desc, out, treelet_min);
   return p.run(traversal);
 }
 

@@ -23,13 +23,16 @@ struct PackedScene {
   bool has_wrappers = false;             // any translation / y-rotation in the scene
   bool has_fast = false;                 // fast_nodes valid
   uint32_t ref_stack_need = 0, fast_stack_need = 0;
+  uint32_t treelets = 0, treelet_prims = 0;   // own-BVH stand-ins inside the reference graph
   uint32_t traversal_used = 0;           // RT_TRAVERSAL_REFERENCE or RT_TRAVERSAL_FAST
   std::map<uint64_t, uint32_t> checker_ids, noise_ids;   // arena offset -> table index (dedup)
   std::string error;
 };
 
 // returns RT_OK or an RT_ERR_* code (text in out.error)
-int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out);
+// treelet_min: RT_TRAVERSAL_AUTO on a scene with wrappers replaces wrapper-free subtrees of the reference BVH that hold
+// at least this many primitives by an own SAH BVH (0 = never)
+int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out, uint32_t treelet_min = 8);
 
 // one reference Material (24 B) -> the two 16-byte words of a device material record, pre-resolving its
 // texture against `arena`; may append to out.checkers / perlin tables.

@@ -149,10 +149,39 @@ __device__ __forceinline__ bool aabb_axis(float lo, float hi, float o, float inv
   return !(t1 <= t0);
 }
 
+// ---- conservative slab test of the two child boxes of an own node (64 B: n0 = c0 x,y; n1 = c1 x,y; n2 = both z) ----
+// Planes as one fma each: t = plane * inv - o * inv.  The rounding of o * inv moves a plane by up to |o * inv| * 2^-24
+// in t, so the overlap test gets 8x that much slack (and a relative one for the fma itself): the cull stays
+// conservative, which is all that exactness of the closest hit needs.  1/d is clamped to a finite value so that a
+// ray parallel to a slab gets -huge/+huge plane distances instead of inf - inf; fminf/fmaxf drop NaNs (0 * inf).
+__device__ __forceinline__ void slab_pair(const float4 n0, const float4 n1, const float4 n2, const V3 inv, const V3 noi,
+                                          const float slack, const float tmin, const float tmax, float &e0, float &e1,
+                                          bool &h0, bool &h1) {
+  const float c0x0 = fmaf(n0.x, inv.x, noi.x), c0x1 = fmaf(n0.y, inv.x, noi.x);
+  const float c0y0 = fmaf(n0.z, inv.y, noi.y), c0y1 = fmaf(n0.w, inv.y, noi.y);
+  const float c0z0 = fmaf(n2.x, inv.z, noi.z), c0z1 = fmaf(n2.y, inv.z, noi.z);
+  const float c1x0 = fmaf(n1.x, inv.x, noi.x), c1x1 = fmaf(n1.y, inv.x, noi.x);
+  const float c1y0 = fmaf(n1.z, inv.y, noi.y), c1y1 = fmaf(n1.w, inv.y, noi.y);
+  const float c1z0 = fmaf(n2.z, inv.z, noi.z), c1z1 = fmaf(n2.w, inv.z, noi.z);
+  e0 = fmaxf(fmaxf(fminf(c0x0, c0x1), fminf(c0y0, c0y1)), fmaxf(fminf(c0z0, c0z1), tmin));
+  float x0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), tmax));
+  e1 = fmaxf(fmaxf(fminf(c1x0, c1x1), fminf(c1y0, c1y1)), fmaxf(fminf(c1z0, c1z1), tmin));
+  float x1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), tmax));
+  x0 = fmaf(x0, 1.000001f, slack); x1 = fmaf(x1, 1.000001f, slack);
+  h0 = e0 <= x0; h1 = e1 <= x1;
+}
+
 // ================= reference-order traversal (instance wrappers, reference BVH, reference visiting order) ======
 // Returns true when something was hit.  The ray is edited in place by the wrappers and, like the reference,
 // comes back with the rounding drift of the un-rotate / un-translate (Q12).
-template <class C>
+//
+// Treelets (K_NONE links with index > 0, planted by the packer): a subtree of the reference's BVH without wrappers
+// below it cannot change the ray, and everything in it is visited before anything after it, so all that the rest
+// of the walk sees of it is (tmax, hit record) when it is left.  That pair is the closest hit of the subtree's
+// primitives within the tmax it was entered with -- independent of the order inside and of conservative culling --
+// so the subtree is walked through an own SAH BVH, near child first, like trace_fast does for a whole scene.
+// TREELETS = false compiles the walk without the own-node case (scenes where the packer planted none).
+template <bool TREELETS, class C>
 __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float tmin, float tmax, Hit &h,
                                                 uint32_t *stk, const int stride, C &cnt) {
   bool result = false, was_last_hit = false, in_translation = false, in_rotation = false;
@@ -160,6 +189,11 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
   stk[0] = sc.ref_root; sp = 1;
   V3 inv = v3(frcp(r.d.x), frcp(r.d.y), frcp(r.d.z));
   float a = dot_xfirst(r.d, r.d);
+  // slab constants of the own nodes (see slab_pair); recomputed after a wrapper moved the ray
+  bool own_ok = false;
+  V3 cinv = inv, noi = inv;
+  float slack = 0.0f;
+  // every item goes through the stack and is popped here: one place where the lanes of a warp meet again
   while (sp > 0) {
     const uint32_t cur = stk[(--sp) * stride];
     const uint32_t idx = rtd::ref_index(cur);
@@ -190,10 +224,11 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
         const float4 x = ldg4(sc.xforms + idx);
         const V3 off = v3(x.x, x.y, x.z);
         cnt.translation();
+        own_ok = false;
         if (!in_translation) {
           was_last_hit = false;
           r.o = vsub(r.o, off);
-          stk[(sp++) * stride] = cur;
+          stk[(sp++) * stride] = cur;                       // comes back as the undo
           stk[(sp++) * stride] = __float_as_uint(x.w);
           in_translation = true;
         } else {
@@ -206,6 +241,7 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
         const float4 x = ldg4(sc.xforms + idx);
         const float sn = x.x, cs = x.y;
         cnt.rotation();
+        own_ok = false;
         if (!in_rotation) {                                 // rt.cu:1194-1209, roundings from the reference's SASS
           was_last_hit = false;
           const V3 o = r.o, d = r.d;
@@ -232,7 +268,30 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
         const uint2 s = __ldg(sc.structures + idx);
         for (uint32_t i = 0; i < s.y; ++i) stk[(sp++) * stride] = __ldg(sc.struct_children + s.x + i);
       } break;
-      default: break;
+      default: {                                            // K_NONE: index 0 = nothing, else node (index - 1) of a treelet
+        if (!TREELETS || idx == 0) break;
+        if (!own_ok) {
+          const float big = 1.0e30f;
+          cinv = v3(fminf(fmaxf(inv.x, -big), big), fminf(fmaxf(inv.y, -big), big), fminf(fmaxf(inv.z, -big), big));
+          noi = v3(-(r.o.x * cinv.x), -(r.o.y * cinv.y), -(r.o.z * cinv.z));
+          slack = fminf((fabsf(noi.x) + fabsf(noi.y) + fabsf(noi.z)) * 4.76837158e-7f, 3.0e38f);
+          own_ok = true;
+        }
+        const float4 *nd = sc.fast_nodes + 4 * (size_t)(idx - 1u);
+        const float4 n0 = ldg4(nd), n1 = ldg4(nd + 1), n2 = ldg4(nd + 2), n3 = ldg4(nd + 3);
+        cnt.box(2);
+        float e0, e1;
+        bool h0, h1;
+        slab_pair(n0, n1, n2, cinv, noi, slack, tmin, tmax, e0, e1, h0, h1);
+        const uint32_t r0 = __float_as_uint(n3.x), r1 = __float_as_uint(n3.y);
+        const bool swap = e1 < e0;                          // near child on top
+        if (h0 && h1) {
+          stk[(sp++) * stride] = swap ? r0 : r1;
+          stk[(sp++) * stride] = swap ? r1 : r0;
+        } else if (h0 || h1) {
+          stk[(sp++) * stride] = h0 ? r0 : r1;
+        }
+      } break;
     }
   }
   return result;
@@ -248,67 +307,11 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
   // the same formulas hit_sphere / hit_planar use (identical bits)
   uint32_t best = 0xffffffffu;
   const float a = dot_xfirst(r.d, r.d);
-  // slab planes as one fma each: t = plane * inv - o * inv.  The rounding of o * inv moves a plane by up to
-  // |o * inv| * 2^-24 in t, so the overlap test gets 8x that much slack (and a relative one for the fma itself):
-  // the cull stays conservative, which is all that exactness of the closest hit needs.  1/d is clamped to a
-  // finite value so that a ray parallel to a slab gets -huge/+huge plane distances instead of inf - inf.
+  // slab constants: see slab_pair
   const float big = 1.0e30f;
   const V3 inv = v3(fminf(fmaxf(frcp(r.d.x), -big), big), fminf(fmaxf(frcp(r.d.y), -big), big), fminf(fmaxf(frcp(r.d.z), -big), big));
   const V3 noi = v3(-(r.o.x * inv.x), -(r.o.y * inv.y), -(r.o.z * inv.z));
   const float slack = fminf((fabsf(noi.x) + fabsf(noi.y) + fabsf(noi.z)) * 4.76837158e-7f, 3.0e38f);
-#ifdef RT_WHILE_WHILE
-  // while-while: walk inner nodes until this lane holds a leaf (lanes re-converge behind the inner loop, so the
-  // primitive tests of a warp run together), test it, pop, repeat
-  int sp = 0;
-  uint32_t cur = sc.fast_root;
-  for (;;) {
-    while (rtd::ref_kind(cur) == rtd::K_BVH) {
-      const uint32_t idx = rtd::ref_index(cur);
-      const float4 n0 = ldg4(sc.fast_nodes + 4 * idx);
-      const float4 n1 = ldg4(sc.fast_nodes + 4 * idx + 1);
-      const float4 n2 = ldg4(sc.fast_nodes + 4 * idx + 2);
-      const float4 n3 = ldg4(sc.fast_nodes + 4 * idx + 3);
-      cnt.box(2);
-      const float c0x0 = fmaf(n0.x, inv.x, noi.x), c0x1 = fmaf(n0.y, inv.x, noi.x);
-      const float c0y0 = fmaf(n0.z, inv.y, noi.y), c0y1 = fmaf(n0.w, inv.y, noi.y);
-      const float c0z0 = fmaf(n2.x, inv.z, noi.z), c0z1 = fmaf(n2.y, inv.z, noi.z);
-      const float c1x0 = fmaf(n1.x, inv.x, noi.x), c1x1 = fmaf(n1.y, inv.x, noi.x);
-      const float c1y0 = fmaf(n1.z, inv.y, noi.y), c1y1 = fmaf(n1.w, inv.y, noi.y);
-      const float c1z0 = fmaf(n2.z, inv.z, noi.z), c1z1 = fmaf(n2.w, inv.z, noi.z);
-      const float e0 = fmaxf(fmaxf(fminf(c0x0, c0x1), fminf(c0y0, c0y1)), fmaxf(fminf(c0z0, c0z1), tmin));
-      float x0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), tmax));
-      const float e1 = fmaxf(fmaxf(fminf(c1x0, c1x1), fminf(c1y0, c1y1)), fmaxf(fminf(c1z0, c1z1), tmin));
-      float x1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), tmax));
-      x0 = fmaf(x0, 1.000001f, slack); x1 = fmaf(x1, 1.000001f, slack);
-      const bool h0 = e0 <= x0, h1 = e1 <= x1;
-      const uint32_t r0 = __float_as_uint(n3.x), r1 = __float_as_uint(n3.y);
-      if (h0 && h1) {
-        const bool swap = e1 < e0;
-        cur = swap ? r1 : r0;
-        stk[(sp++) * stride] = swap ? r0 : r1;
-      } else if (h0 || h1) {
-        cur = h0 ? r0 : r1;
-      } else if (sp > 0) {
-        cur = stk[(--sp) * stride];
-      } else {
-        cur = 0xffffffffu;                                // nothing left: K_NONE with every index bit set
-      }
-    }
-    if (cur == 0xffffffffu) break;
-    const uint32_t kind = rtd::ref_kind(cur), idx = rtd::ref_index(cur);
-    if (kind == rtd::K_SPHERE) {
-      cnt.sphere();
-      float root;
-      if (sphere_root(sc, idx, r, a, tmin, tmax, root)) { tmax = root; best = cur; }
-    } else if (kind == rtd::K_QUAD || kind == rtd::K_TRIANGLE) {
-      cnt.planar();
-      float tt;
-      if (planar_t(sc, idx, kind == rtd::K_TRIANGLE, r, tmin, tmax, tt)) { tmax = tt; best = cur; }
-    }                                                     // K_NONE index 0: the empty second child of a one-primitive scene
-    if (sp == 0) break;
-    cur = stk[(--sp) * stride];
-  }
-#else
   int sp = 0;
   uint32_t cur = sc.fast_root;
   for (;;) {
@@ -320,19 +323,9 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
       const float4 n2 = ldg4(sc.fast_nodes + 4 * idx + 2);
       const float4 n3 = ldg4(sc.fast_nodes + 4 * idx + 3);
       cnt.box(2);
-      // slab test of both children; fminf/fmaxf drop NaNs (0*inf) which keeps the test conservative
-      const float c0x0 = fmaf(n0.x, inv.x, noi.x), c0x1 = fmaf(n0.y, inv.x, noi.x);
-      const float c0y0 = fmaf(n0.z, inv.y, noi.y), c0y1 = fmaf(n0.w, inv.y, noi.y);
-      const float c0z0 = fmaf(n2.x, inv.z, noi.z), c0z1 = fmaf(n2.y, inv.z, noi.z);
-      const float c1x0 = fmaf(n1.x, inv.x, noi.x), c1x1 = fmaf(n1.y, inv.x, noi.x);
-      const float c1y0 = fmaf(n1.z, inv.y, noi.y), c1y1 = fmaf(n1.w, inv.y, noi.y);
-      const float c1z0 = fmaf(n2.z, inv.z, noi.z), c1z1 = fmaf(n2.w, inv.z, noi.z);
-      const float e0 = fmaxf(fmaxf(fminf(c0x0, c0x1), fminf(c0y0, c0y1)), fmaxf(fminf(c0z0, c0z1), tmin));
-      float x0 = fminf(fminf(fmaxf(c0x0, c0x1), fmaxf(c0y0, c0y1)), fminf(fmaxf(c0z0, c0z1), tmax));
-      const float e1 = fmaxf(fmaxf(fminf(c1x0, c1x1), fminf(c1y0, c1y1)), fmaxf(fminf(c1z0, c1z1), tmin));
-      float x1 = fminf(fminf(fmaxf(c1x0, c1x1), fmaxf(c1y0, c1y1)), fminf(fmaxf(c1z0, c1z1), tmax));
-      x0 = fmaf(x0, 1.000001f, slack); x1 = fmaf(x1, 1.000001f, slack);
-      const bool h0 = e0 <= x0, h1 = e1 <= x1;
+      float e0, e1;
+      bool h0, h1;
+      slab_pair(n0, n1, n2, inv, noi, slack, tmin, tmax, e0, e1, h0, h1);
       const uint32_t r0 = __float_as_uint(n3.x), r1 = __float_as_uint(n3.y);
       if (h0 && h1) {
         const bool swap = e1 < e0;
@@ -355,7 +348,6 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
     if (sp == 0) break;
     cur = stk[(--sp) * stride];
   }
-#endif
   if (best == 0xffffffffu) return false;
   if (rtd::ref_kind(best) == rtd::K_SPHERE) sphere_record(sc, rtd::ref_index(best), r, tmax, h);
   else planar_record(sc, rtd::ref_index(best), r, tmax, h);
