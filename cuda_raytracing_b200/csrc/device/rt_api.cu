@@ -56,12 +56,13 @@ struct rt_context {
   bool has_scene = false;
   rtd::Scene scene{};
   rtp::PackedScene packed;
-  DeviceBuffer b_ref_nodes, b_xforms, b_structs, b_struct_children, b_fast_nodes, b_spheres, b_planars, b_materials,
+  DeviceBuffer b_ref_nodes, b_xforms, b_instances, b_structs, b_struct_children, b_fast_nodes, b_spheres, b_planars, b_materials,
       b_checkers, b_perlin_vec, b_perlin_perm, b_arena;
   // rng
   DeviceBuffer b_rng_mats, b_rng_init, b_rng_states, b_progress, b_counters;   // b_rng_init: pristine states (cache)
   int chunk_samples = 0;                                   // 0 = automatic; env RT_CHUNK overrides (tuning knob)
   int claim_group = 0;                                     // 0 = automatic; env RT_CLAIM_GROUP (tuning knob)
+  uint32_t fuse_min = 8;                                   // env RT_FUSE_MIN: wrapper chains around one object become one item when there are this many (0 = never)
   uint32_t treelet_min = 8;                                // env RT_TREELET_MIN: smallest wrapper-free subtree given an own BVH (0 = none)
   int tile_w = 8;                                          // work items walk 8x4-pixel tiles; env RT_TILE_W (1..32, power of 2)
   uint64_t rng_seed = 0, rng_first = 0, rng_count = 0; bool rng_valid = false;
@@ -105,6 +106,7 @@ int rt_context_create(int device_id, rt_context **out) {
   for (int i = 0; i < 4; ++i) cudaEventCreate(&ctx->ev[i]);
   if (const char *v = getenv("RT_CHUNK")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 24)) ctx->chunk_samples = (int)x; }
   if (const char *v = getenv("RT_TILE_W")) { const long x = strtol(v, nullptr, 10); if (x >= 1 && x <= 32 && (x & (x - 1)) == 0) ctx->tile_w = (int)x; }
+  if (const char *v = getenv("RT_FUSE_MIN")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 30)) ctx->fuse_min = (uint32_t)x; }
   if (const char *v = getenv("RT_TREELET_MIN")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 30)) ctx->treelet_min = (uint32_t)x; }
   if (const char *v = getenv("RT_CLAIM_GROUP")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= 32) ctx->claim_group = (int)x; }
   std::vector<uint32_t> mats;
@@ -121,7 +123,7 @@ void rt_context_destroy(rt_context *ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  DeviceBuffer *all[] = {&ctx->b_ref_nodes, &ctx->b_xforms, &ctx->b_structs, &ctx->b_struct_children, &ctx->b_fast_nodes,
+  DeviceBuffer *all[] = {&ctx->b_ref_nodes, &ctx->b_xforms, &ctx->b_instances, &ctx->b_structs, &ctx->b_struct_children, &ctx->b_fast_nodes,
                          &ctx->b_spheres, &ctx->b_planars, &ctx->b_materials, &ctx->b_checkers, &ctx->b_perlin_vec,
                          &ctx->b_perlin_perm, &ctx->b_arena, &ctx->b_rng_mats, &ctx->b_rng_init, &ctx->b_rng_states,
                          &ctx->b_progress, &ctx->b_counters,
@@ -157,17 +159,18 @@ int rt_scene_upload(rt_context *ctx, const rt_scene_desc *desc, uint32_t travers
   ctx->has_scene = false;
   ctx->packed = rtp::PackedScene();
   rtp::PackedScene &p = ctx->packed;
-  int rc = rtp::pack_scene(*desc, traversal, p, ctx->treelet_min);
+  int rc = rtp::pack_scene(*desc, traversal, p, ctx->treelet_min, ctx->fuse_min);
   if (rc != RT_OK) return fail(ctx, rc, p.error);
   cudaStream_t s = ctx->stream;
 #define UP(buf, vec) RT_CUDA(ctx, ctx->buf.upload((vec).data(), (vec).size() * sizeof((vec)[0]), s))
-  UP(b_ref_nodes, p.ref_nodes); UP(b_xforms, p.xforms); UP(b_structs, p.structures); UP(b_struct_children, p.struct_children);
+  UP(b_ref_nodes, p.ref_nodes); UP(b_xforms, p.xforms); UP(b_instances, p.instances); UP(b_structs, p.structures); UP(b_struct_children, p.struct_children);
   UP(b_fast_nodes, p.fast_nodes); UP(b_spheres, p.spheres); UP(b_planars, p.planars); UP(b_materials, p.materials);
   UP(b_checkers, p.checkers); UP(b_perlin_vec, p.perlin_vectors); UP(b_perlin_perm, p.perlin_perm); UP(b_arena, p.tex_arena);
 #undef UP
   RT_CUDA(ctx, cudaStreamSynchronize(s));       // the host vectors may be reused after return
   rtd::Scene &sc = ctx->scene;
   sc.ref_nodes = (const float4 *)ctx->b_ref_nodes.ptr; sc.xforms = (const float4 *)ctx->b_xforms.ptr;
+  sc.instances = (const float4 *)ctx->b_instances.ptr;
   sc.structures = (const uint2 *)ctx->b_structs.ptr; sc.struct_children = (const uint32_t *)ctx->b_struct_children.ptr;
   sc.ref_root = p.ref_root; sc.fast_nodes = (const float4 *)ctx->b_fast_nodes.ptr; sc.fast_root = p.fast_root;
   sc.spheres = (const float4 *)ctx->b_spheres.ptr; sc.planars = (const float4 *)ctx->b_planars.ptr;
@@ -264,7 +267,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   a.count_rays = (p->flags & (RT_RENDER_COUNT_RAYS | RT_RENDER_COUNT_OPS)) ? 1u : 0u;
   a.count_ops = (p->flags & RT_RENDER_COUNT_OPS) ? 1u : 0u;
   // kernel variant: 1 = own BVH over the whole scene, 2 = reference order with treelets, 0 = reference order
-  const int mode = ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? 1 : (ctx->packed.treelets > 0 ? 2 : 0);
+  const int mode = ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? 1 : (ctx->packed.treelets + ctx->packed.fused_instances > 0 ? 2 : 0);
   RT_CUDA(ctx, rtk::launch_render(a, mode, ctx->sm_count, s, &ctx->last_launch));
   ++launches;
   if (stats) {

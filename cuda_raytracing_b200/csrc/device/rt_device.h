@@ -39,6 +39,12 @@ RTD_HD uint32_t ref_index(uint32_t r) { return r & INDEX_MASK; }
 // `fast_nodes` -- an own SAH BVH that stands in for a wrapper-free subtree of the reference's BVH (index 0 stays
 // "nothing": the empty second child of a one-primitive scene).
 RTD_HD uint32_t make_own_ref(uint32_t node) { return (K_NONE << KIND_SHIFT) | (node + 1u); }
+// Fused instances: a K_NONE link with INSTANCE_BIT set points at record (index & ~INSTANCE_BIT) of `instances` -- a
+// translation and/or y-rotation around one primitive or one structure of primitives, done as ONE item of the walk
+// (enter, test, leave: the same operations in the same order as the wrapper items it replaces).
+constexpr uint32_t INSTANCE_BIT = 1u << 28;
+RTD_HD uint32_t make_instance_ref(uint32_t i) { return (K_NONE << KIND_SHIFT) | INSTANCE_BIT | i; }
+constexpr uint32_t INST_TRANSLATE = 1u, INST_ROTATE = 2u;
 
 // material record: 2 x 16 B per primitive (prim id = sphere index, or sphere_count + planar index) -------
 enum MatType : uint32_t { M_LAMBERTIAN = 0, M_METAL = 1, M_DIELECTRIC = 2, M_DIFFUSE_LIGHT = 3 };   // rt.cu:79-84
@@ -57,6 +63,7 @@ struct Scene {
   const float4 *xforms;         // 1 per wrapper: translation {ox,oy,oz, child ref}; y-rotation {sin,cos,0, child ref}
   const uint2 *structures;      // {first child slot, count}
   const uint32_t *struct_children;
+  const float4 *instances;      // 2 per fused instance: {offset.xyz, child ref} {sin, cos, INST_* flags, 0}
   uint32_t ref_root;            // tagged ref of the reference's root BVH node
   // own BVH over world-space primitives (RT_TRAVERSAL_FAST): 4 x float4 per node
   //   n0 = {c0.x0, c0.x1, c0.y0, c0.y1}  n1 = {c1.x0, c1.x1, c1.y0, c1.y1}

@@ -167,7 +167,9 @@ struct Packer {
   std::vector<rt_material> sphere_mats, planar_mats;
   std::vector<Leaf> leaves;                     // FAST traversal leaves
   uint32_t treelet_min;                         // smallest wrapper-free subtree (primitives) worth an own BVH; 0 = never
-  Packer(const rt_scene_desc &desc, PackedScene &o, uint32_t tmin) : d(desc), out(o), treelet_min(tmin) {}
+  bool fuse_instances;
+  uint32_t fuse_min;                            // fewer qualifying chains than this (and no treelet): keep the plain walk
+  Packer(const rt_scene_desc &desc, PackedScene &o, uint32_t tmin, uint32_t fmin) : d(desc), out(o), treelet_min(tmin), fuse_instances(fmin > 0), fuse_min(fmin) {}
 
   const rt_hittable &H(uint32_t i) const { return d.hittables[i]; }
 
@@ -195,6 +197,7 @@ struct Packer {
   // worked on): `base` = entries below this subtree's root
   uint32_t stack_need(uint32_t href, uint32_t base, int guard) const {
     if (guard > 64 || href >= d.hittable_count) return base;
+    if (fused[href]) return base + fused[href] - 1;                        // nothing pushed, or the way out + a structure's children
     if (treelet_depth[href] > 0) return base + treelet_depth[href] + 1;    // one pending far child per level + the pair pushed last
     const rt_hittable &h = H(href);
     switch (h.type) {
@@ -286,6 +289,57 @@ struct Packer {
     } else if (h.type == RT_OBJ_STRUCTURE && (uint64_t)h.u.structure.first + h.u.structure.count <= d.hittable_count) {
       for (uint32_t k = 0; k < h.u.structure.count; ++k) plant_treelets(h.u.structure.first + k, min_prims, guard + 1);
     }
+  }
+  // ---- fused instances: T(R(x)), T(x), R(x) around a primitive or a structure of primitives, reached from the BVH only ----
+  std::vector<uint8_t> fused;
+  bool is_prim(uint32_t href) const {
+    return href < d.hittable_count && (H(href).type == RT_OBJ_SPHERE || H(href).type == RT_OBJ_TRIANGLE || H(href).type == RT_OBJ_QUAD);
+  }
+  bool fusable_child(uint32_t href) const {
+    if (is_prim(href)) return true;
+    if (href >= d.hittable_count || H(href).type != RT_OBJ_STRUCTURE) return false;
+    const rt_structure &st = H(href).u.structure;
+    if (st.count == 0 || st.count > 64 || (uint64_t)st.first + st.count > d.hittable_count) return false;
+    for (uint32_t k = 0; k < st.count; ++k) if (!is_prim(st.first + k)) return false;
+    return true;
+  }
+  uint32_t plant_instances(bool dry_run) {             // returns the number of chains that qualify
+    uint32_t found = 0;
+    const uint64_t n = d.hittable_count;
+    std::vector<uint8_t> nested(n, 0);              // referenced from inside a wrapper or a structure
+    for (uint64_t i = 0; i < n; ++i) {
+      const rt_hittable &h = H((uint32_t)i);
+      if (h.type == RT_OBJ_TRANSLATION && h.u.translation.child < n) nested[h.u.translation.child] = 1;
+      else if (h.type == RT_OBJ_Y_ROTATION && h.u.y_rotation.child < n) nested[h.u.y_rotation.child] = 1;
+      else if (h.type == RT_OBJ_STRUCTURE && (uint64_t)h.u.structure.first + h.u.structure.count <= n)
+        for (uint32_t k = 0; k < h.u.structure.count; ++k) nested[h.u.structure.first + k] = 1;
+    }
+    for (uint64_t i = 0; i < n; ++i) {
+      const rt_hittable &h = H((uint32_t)i);
+      if (nested[i]) continue;
+      uint32_t flags = 0, child = 0;
+      float ox = 0, oy = 0, oz = 0, sn = 0, cs = 1;
+      if (h.type == RT_OBJ_TRANSLATION && h.u.translation.child < n) {
+        flags = INST_TRANSLATE; child = h.u.translation.child;
+        ox = h.u.translation.offset.x; oy = h.u.translation.offset.y; oz = h.u.translation.offset.z;
+        if (H(child).type == RT_OBJ_Y_ROTATION && H(child).u.y_rotation.child < n) {
+          flags |= INST_ROTATE; sn = H(child).u.y_rotation.sin_theta; cs = H(child).u.y_rotation.cos_theta;
+          child = H(child).u.y_rotation.child;
+        }
+      } else if (h.type == RT_OBJ_Y_ROTATION && h.u.y_rotation.child < n) {
+        flags = INST_ROTATE; child = h.u.y_rotation.child; sn = h.u.y_rotation.sin_theta; cs = h.u.y_rotation.cos_theta;
+      } else continue;
+      if (!fusable_child(child)) continue;
+      ++found;
+      if (dry_run) continue;
+      const uint32_t k = (uint32_t)(out.instances.size() / 2);
+      out.instances.push_back(f4(ox, oy, oz, as_float(tag[child])));
+      out.instances.push_back(f4(sn, cs, as_float(flags), 0.0f));
+      tag[i] = make_instance_ref(k);
+      fused[i] = (uint8_t)(1 + (is_prim(child) ? 0 : 1 + (uint32_t)H(child).u.structure.count));
+      ++out.fused_instances;
+    }
+    return found;
   }
   static void center_leaf(Leaf &lf) { for (int a = 0; a < 3; ++a) lf.centroid[a] = 0.5f * (lf.box.lo[a] + lf.box.hi[a]); }
 
@@ -385,10 +439,14 @@ struct Packer {
       }
     }
     // wrapper-free subtrees of the reference BVH -> own SAH treelets (their roots' tags change before links are written)
-    pure_prims.assign(n, -2); treelet_depth.assign(n, 0);
+    pure_prims.assign(n, -2); treelet_depth.assign(n, 0); fused.assign(n, 0);
     const bool want_fast = traversal == RT_TRAVERSAL_FAST || (traversal == RT_TRAVERSAL_AUTO && !out.has_wrappers);
     if (traversal == RT_TRAVERSAL_AUTO && out.has_wrappers && treelet_min > 0 && d.world_refs[d.root_wref] < n)
       plant_treelets(d.world_refs[d.root_wref], treelet_min, 0);
+    // measured (profiles/r1_configs_treelets.jsonl): the walk with the extra cases only pays when it has work to do --
+    // a Cornell box with two instances is faster through the plain reference-order kernel
+    if (traversal == RT_TRAVERSAL_AUTO && out.has_wrappers && fuse_instances &&
+        (out.treelets > 0 || plant_instances(true) >= fuse_min)) plant_instances(false);
     // pass 2: links
     out.ref_nodes.resize(2 * (size_t)n_bvh); out.xforms.resize(n_xf); out.structures.resize(n_st);
     for (uint64_t i = 0; i < n; ++i) {
@@ -400,6 +458,8 @@ struct Packer {
         const rt_aabb &b = h.u.bvh.bbox;
         out.ref_nodes[2 * idx] = f4(b.x0, b.x1, b.y0, b.y1);
         out.ref_nodes[2 * idx + 1] = f4(b.z0, b.z1, as_float(tag[d.world_refs[h.u.bvh.left]]), as_float(tag[d.world_refs[h.u.bvh.right]]));
+      } else if (fused[i]) {
+        continue;                                          // a fused instance: its record is in out.instances
       } else if (h.type == RT_OBJ_TRANSLATION) {
         if (h.u.translation.child >= n) { out.error = "rt_scene_upload: wrapper child out of range"; return RT_ERR_INVALID; }
         out.xforms[idx] = f4(h.u.translation.offset.x, h.u.translation.offset.y, h.u.translation.offset.z, as_float(tag[h.u.translation.child]));
@@ -461,9 +521,9 @@ struct Packer {
 
 }  // namespace
 
-int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out, uint32_t treelet_min) {
+int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out, uint32_t treelet_min, uint32_t fuse_min) {
   if (traversal > RT_TRAVERSAL_FAST) { out.error = "rt_scene_upload: unknown traversal mode"; return RT_ERR_INVALID; }
-  Packer p(desc, out, treelet_min);
+  Packer p(desc, out, treelet_min, fuse_min);
   return p.run(traversal);
 }
 

@@ -13,7 +13,7 @@
 namespace rtp {
 
 struct PackedScene {
-  std::vector<float4> ref_nodes, xforms, fast_nodes, spheres, planars, checkers, perlin_vectors;
+  std::vector<float4> ref_nodes, xforms, instances, fast_nodes, spheres, planars, checkers, perlin_vectors;
   std::vector<uint2> structures;
   std::vector<uint32_t> struct_children;
   std::vector<uint4> materials;          // 2 per primitive id
@@ -24,6 +24,7 @@ struct PackedScene {
   bool has_fast = false;                 // fast_nodes valid
   uint32_t ref_stack_need = 0, fast_stack_need = 0;
   uint32_t treelets = 0, treelet_prims = 0;   // own-BVH stand-ins inside the reference graph
+  uint32_t fused_instances = 0;               // wrapper chains around one primitive / structure done as one item
   uint32_t traversal_used = 0;           // RT_TRAVERSAL_REFERENCE or RT_TRAVERSAL_FAST
   std::map<uint64_t, uint32_t> checker_ids, noise_ids;   // arena offset -> table index (dedup)
   std::string error;
@@ -32,7 +33,10 @@ struct PackedScene {
 // returns RT_OK or an RT_ERR_* code (text in out.error)
 // treelet_min: RT_TRAVERSAL_AUTO on a scene with wrappers replaces wrapper-free subtrees of the reference BVH that hold
 // at least this many primitives by an own SAH BVH (0 = never)
-int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out, uint32_t treelet_min = 8);
+// fuse_min: the same mode does translation / y-rotation chains around one object as one item of the walk when the scene
+// has a treelet or at least this many such chains (0 = never)
+int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out, uint32_t treelet_min = 8,
+               uint32_t fuse_min = 8);
 
 // one reference Material (24 B) -> the two 16-byte words of a device material record, pre-resolving its
 // texture against `arena`; may append to out.checkers / perlin tables.

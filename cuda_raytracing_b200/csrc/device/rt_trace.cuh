@@ -180,7 +180,12 @@ __device__ __forceinline__ void slab_pair(const float4 n0, const float4 n1, cons
 // of the walk sees of it is (tmax, hit record) when it is left.  That pair is the closest hit of the subtree's
 // primitives within the tmax it was entered with -- independent of the order inside and of conservative culling --
 // so the subtree is walked through an own SAH BVH, near child first, like trace_fast does for a whole scene.
-// TREELETS = false compiles the walk without the own-node case (scenes where the packer planted none).
+//
+// Fused instances (K_NONE links with INSTANCE_BIT): translate / rotate / test / un-rotate / un-translate of one wrapped
+// primitive as one item -- the operations of the wrapper items, in their order, without five trips through the
+// stack; around a structure the way in and the way out are one item each.
+//
+// TREELETS = false compiles the walk without the K_NONE case (scenes where the packer planted neither).
 template <bool TREELETS, class C>
 __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float tmin, float tmax, Hit &h,
                                                 uint32_t *stk, const int stride, C &cnt) {
@@ -270,6 +275,63 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
       } break;
       default: {                                            // K_NONE: index 0 = nothing, else node (index - 1) of a treelet
         if (!TREELETS || idx == 0) break;
+        if (idx & rtd::INSTANCE_BIT) {
+          const float4 *rec = sc.instances + 2 * (size_t)(idx & ~rtd::INSTANCE_BIT);
+          const float4 i0 = ldg4(rec), i1 = ldg4(rec + 1);
+          const uint32_t fl = __float_as_uint(i1.z);
+          const V3 off = v3(i0.x, i0.y, i0.z);
+          const float sn = i1.x, cs = i1.y;
+          bool hit_in;                                      // was_last_hit: cleared by the entries, set by a hit inside
+          own_ok = false;
+          if (!(in_translation || in_rotation)) {           // enter (instances are only planted outside any wrapper)
+            if (fl & rtd::INST_TRANSLATE) { cnt.translation(); r.o = vsub(r.o, off); }
+            if (fl & rtd::INST_ROTATE) {                    // rt.cu:1194-1209
+              cnt.rotation();
+              const V3 o = r.o, d = r.d;
+              r.o = v3(ffma(o.x, cs, -fmul(o.z, sn)), o.y, ffma(o.x, sn, fmul(o.z, cs)));
+              r.d = v3(ffma(d.x, cs, -fmul(d.z, sn)), d.y, ffma(d.z, cs, fmul(d.x, sn)));
+              a = dot_xfirst(r.d, r.d);
+            }
+            const uint32_t child = __float_as_uint(i0.w);
+            const uint32_t ck = rtd::ref_kind(child), ci = rtd::ref_index(child);
+            if (ck == rtd::K_STRUCTURE) {
+              // a structure's primitives go through the stack like any other (they share the primitive cases with the
+              // rest of the warp); this link comes back after them as the way out
+              const uint2 st = __ldg(sc.structures + ci);
+              was_last_hit = false;
+              in_translation = (fl & rtd::INST_TRANSLATE) != 0; in_rotation = (fl & rtd::INST_ROTATE) != 0;
+              stk[(sp++) * stride] = cur;
+              for (uint32_t i = 0; i < st.y; ++i) stk[(sp++) * stride] = __ldg(sc.struct_children + st.x + i);
+              break;
+            }
+            if (ck == rtd::K_SPHERE) { cnt.sphere(); hit_in = hit_sphere(sc, ci, r, a, tmin, tmax, h); }
+            else { cnt.planar(); hit_in = hit_planar(sc, ci, ck == rtd::K_TRIANGLE, r, tmin, tmax, h); }
+            if (hit_in) result = true;
+          } else {                                          // the way out of a structure instance
+            hit_in = was_last_hit;
+            in_translation = false; in_rotation = false;
+          }
+          if (fl & rtd::INST_ROTATE) {                      // rt.cu:1210-1236
+            cnt.rotation();
+            const V3 o = r.o, d = r.d;
+            r.o = v3(ffma(o.x, cs, fmul(o.z, sn)), o.y, ffma(o.z, cs, -fmul(o.x, sn)));
+            r.d = v3(ffma(d.x, cs, fmul(d.z, sn)), d.y, ffma(d.z, cs, -fmul(d.x, sn)));
+            if (hit_in) {
+              const V3 p = h.p, n = h.n;
+              h.p = v3(ffma(p.x, cs, fmul(p.z, sn)), p.y, ffma(p.z, cs, -fmul(p.x, sn)));
+              h.n = v3(ffma(n.x, cs, fmul(n.z, sn)), n.y, ffma(n.z, cs, -fmul(n.x, sn)));
+            }
+            inv.x = frcp(r.d.x); inv.z = frcp(r.d.z);
+            a = dot_xfirst(r.d, r.d);
+          }
+          if (fl & rtd::INST_TRANSLATE) {
+            cnt.translation();
+            r.o = vadd(r.o, off);
+            if (hit_in) h.p = vadd(h.p, off);
+          }
+          was_last_hit = hit_in;
+          break;
+        }
         if (!own_ok) {
           const float big = 1.0e30f;
           cinv = v3(fminf(fmaxf(inv.x, -big), big), fminf(fmaxf(inv.y, -big), big), fminf(fmaxf(inv.z, -big), big));

@@ -315,3 +315,45 @@ def test_image_does_not_depend_on_scheduling_knobs(product_lib):
     for img in images[1:]:
         assert np.array_equal(common.bits(img), common.bits(images[0]))
     hs.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sid", sorted(WRAPPER_SCENES))
+def test_hybrid_walk_equals_reference_order(product_lib, sid):
+    """RT_TRAVERSAL_AUTO on scenes with instance wrappers: treelets (own BVH inside wrapper-free subtrees) and fused
+    instances, forced on even where the packer would not bother, give the image of the literal reference-order walk
+    bit for bit -- and probes return the same hits and the same edited rays."""
+    hs = product_lib.HostScene(sid)
+    p = hs.params(96, 6, 12)
+    rng = np.random.default_rng(4242 + sid)
+    o, d, t = common.scene_rays(hs.settings, rng, 4000)
+    saved = {k: os.environ.get(k) for k in ("RT_FUSE_MIN", "RT_TREELET_MIN")}
+    results = []
+    try:
+        for knobs, trav in (({}, product_lib.RT_TRAVERSAL_REFERENCE), ({"RT_FUSE_MIN": "1", "RT_TREELET_MIN": "2"}, product_lib.RT_TRAVERSAL_AUTO),
+                            ({"RT_FUSE_MIN": "0", "RT_TREELET_MIN": "3"}, product_lib.RT_TRAVERSAL_AUTO)):
+            for k in saved:
+                os.environ.pop(k, None)
+            os.environ.update(knobs)
+            ctx = product_lib.Context(0)
+            ctx.upload(hs, trav)
+            img, _, st = ctx.render(p)
+            assert st.traversal_used == product_lib.RT_TRAVERSAL_REFERENCE
+            probes = ctx.probe_trace(o, d, t)
+            results.append((img, probes))
+            ctx.close()
+    finally:
+        for k, v in saved.items():
+            os.environ.pop(k, None)
+            if v is not None:
+                os.environ[k] = v
+    img0, pr0 = results[0]
+    for img, pr in results[1:]:
+        assert np.array_equal(common.bits(img), common.bits(img0)), sid
+        for i in range(0, len(pr0), 7):
+            a, b = pr0[i], pr[i]
+            assert a.hit == b.hit, (sid, i)
+            assert list(a.origin[:]) == list(b.origin[:]) and list(a.direction[:]) == list(b.direction[:]), (sid, i)
+            if a.hit:
+                assert a.t == b.t and list(a.point[:]) == list(b.point[:]) and list(a.normal[:]) == list(b.normal[:]), (sid, i)
+    hs.close()
