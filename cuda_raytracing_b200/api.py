@@ -56,7 +56,8 @@ class RenderParams(C.Structure):  # rt_render_params
                 ("pixel_delta_v", C.c_float * 3), ("pixel_delta_u", C.c_float * 3), ("camera_pos", C.c_float * 3),
                 ("defocus_disk_u", C.c_float * 3), ("defocus_disk_v", C.c_float * 3), ("pixel00", C.c_float * 3),
                 ("seed", C.c_uint64), ("subsequence_offset", C.c_uint64), ("row_begin", C.c_int32),
-                ("row_end", C.c_int32), ("flags", C.c_uint32), ("reserved", C.c_uint32)]
+                ("row_end", C.c_int32), ("flags", C.c_uint32), ("band_rows", C.c_uint32), ("band_period", C.c_uint32),
+                ("band_phase", C.c_uint32)]
 
 
 class Stats(C.Structure):  # rt_stats

@@ -65,7 +65,7 @@ struct rt_context {
   uint32_t fuse_min = 8;                                   // env RT_FUSE_MIN: wrapper chains around one object become one item when there are this many (0 = never)
   uint32_t treelet_min = 8;                                // env RT_TREELET_MIN: smallest wrapper-free subtree given an own BVH (0 = none)
   int tile_w = 8;                                          // work items walk 8x4-pixel tiles; env RT_TILE_W (1..32, power of 2)
-  uint64_t rng_seed = 0, rng_first = 0, rng_count = 0; bool rng_valid = false;
+  uint64_t rng_seed = 0, rng_first = 0, rng_count = 0, rng_bands = 0; bool rng_valid = false;
   // scratch for rt_render (host-buffer path)
   DeviceBuffer b_pixels, b_rgb8;
   rtk::LaunchInfo last_launch{};
@@ -203,19 +203,47 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   if (!d_pixels) return fail(ctx, RT_ERR_INVALID, "rt_render_device: d_pixels_rgb is NULL");
   RT_CUDA(ctx, cudaSetDevice(ctx->device));
   cudaStream_t s = ctx->stream;
-  const uint64_t first_pixel = (uint64_t)row0 * p->img_width, count = (uint64_t)(row1 - row0) * p->img_width;
+  // the rendered set: a run of rows, or interleaved bands of rows (tile sharding in one launch)
+  const bool banded = p->band_rows > 0 && p->band_period > 1;
+  uint32_t set_rows = (uint32_t)(row1 - row0);
+  if (banded) {
+    if (p->band_phase >= p->band_period) return fail(ctx, RT_ERR_INVALID, "rt_render: band_phase must be below band_period");
+    if (row0 != 0 || row1 != p->img_height) return fail(ctx, RT_ERR_INVALID, "rt_render: row bands need the whole row range");
+    set_rows = 0;
+    for (uint64_t b = p->band_phase; b * p->band_rows < (uint64_t)p->img_height; b += p->band_period) {
+      const uint64_t lo = b * p->band_rows, hi = lo + p->band_rows;
+      set_rows += (uint32_t)((hi < (uint64_t)p->img_height ? hi : (uint64_t)p->img_height) - lo);
+    }
+    if (set_rows == 0) {                                   // more ranks than bands: nothing to do for this one
+      if (stats) { memset(stats, 0, sizeof(*stats)); stats->traversal_used = ctx->packed.traversal_used; }
+      return RT_OK;
+    }
+  }
+  const uint64_t first_pixel = banded ? 0 : (uint64_t)row0 * p->img_width, count = (uint64_t)set_rows * p->img_width;
   const uint64_t first_sub = first_pixel + p->subsequence_offset;
+  const uint64_t band_key = banded ? ((uint64_t)p->band_rows << 40) ^ ((uint64_t)p->band_period << 20) ^ p->band_phase ^ (1ull << 63) : 0;
 
   uint32_t launches = 0;
   if (stats) RT_CUDA(ctx, cudaEventRecord(ctx->ev[0], s));
   const bool cached = ctx->rng_valid && ctx->rng_seed == p->seed && ctx->rng_first == first_sub && ctx->rng_count == count &&
-                      !(p->flags & RT_RENDER_NO_RNG_CACHE);
+                      ctx->rng_bands == band_key && !(p->flags & RT_RENDER_NO_RNG_CACHE);
   if (!cached) {
     RT_CUDA(ctx, ctx->b_rng_init.reserve(count * 6 * sizeof(uint32_t)));
-    RT_CUDA(ctx, rtk::launch_rng_init(p->seed, first_sub, count, (const uint32_t *)ctx->b_rng_mats.ptr,
-                                      (uint32_t *)ctx->b_rng_init.ptr, s));
-    ctx->rng_seed = p->seed; ctx->rng_first = first_sub; ctx->rng_count = count; ctx->rng_valid = true;
-    ++launches;
+    if (!banded) {
+      RT_CUDA(ctx, rtk::launch_rng_init(p->seed, first_sub, count, (const uint32_t *)ctx->b_rng_mats.ptr,
+                                        (uint32_t *)ctx->b_rng_init.ptr, s));
+      ++launches;
+    } else {                                               // one run of consecutive subsequences per band
+      uint64_t done = 0;
+      for (uint64_t b = p->band_phase; b * p->band_rows < (uint64_t)p->img_height; b += p->band_period) {
+        const uint64_t lo = b * p->band_rows, hi = lo + p->band_rows;
+        const uint64_t n = ((hi < (uint64_t)p->img_height ? hi : (uint64_t)p->img_height) - lo) * p->img_width;
+        RT_CUDA(ctx, rtk::launch_rng_init(p->seed, lo * p->img_width + p->subsequence_offset, n, (const uint32_t *)ctx->b_rng_mats.ptr,
+                                          (uint32_t *)ctx->b_rng_init.ptr + 6 * done, s));
+        done += n; ++launches;
+      }
+    }
+    ctx->rng_seed = p->seed; ctx->rng_first = first_sub; ctx->rng_count = count; ctx->rng_bands = band_key; ctx->rng_valid = true;
   }
   // the render kernel advances the states chunk by chunk: it works on a copy, the initial states stay cached
   RT_CUDA(ctx, ctx->b_rng_states.reserve(count * 6 * sizeof(uint32_t)));
@@ -244,9 +272,10 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
     if (chunk > spp) chunk = spp;
     a.chunk_samples = chunk;
     a.chunk_count = (spp + chunk - 1) / chunk;
-    const uint32_t tw = (uint32_t)ctx->tile_w, th = 32u / tw, rows = (uint32_t)(row1 - row0);
+    const uint32_t tw = (uint32_t)ctx->tile_w, th = 32u / tw, rows = set_rows;
     a.tile_shift = 0; while ((1u << a.tile_shift) < tw) ++a.tile_shift;
     a.first_row = row0;
+    if (banded) { a.band_rows = (int32_t)p->band_rows; a.band_period = (int32_t)p->band_period; a.band_phase = (int32_t)p->band_phase; }
     a.tiles_x = ((uint32_t)p->img_width + tw - 1) / tw;
     a.slots_per_chunk = a.tiles_x * ((rows + th - 1) / th) * 32u;
     a.item_count = (unsigned long long)a.slots_per_chunk * (unsigned long long)a.chunk_count;
@@ -307,7 +336,7 @@ int rt_render(rt_context *ctx, const rt_render_params *p, float *h_pixels, uint8
   const uint64_t n = (uint64_t)p->img_width * p->img_height;
   RT_CUDA(ctx, ctx->b_pixels.reserve(n * 3 * sizeof(float)));
   RT_CUDA(ctx, ctx->b_rgb8.reserve(n * 3 + 16));
-  if (row1 - row0 != p->img_height) RT_CUDA(ctx, cudaMemsetAsync(ctx->b_pixels.ptr, 0, n * 3 * sizeof(float), ctx->stream));
+  if (row1 - row0 != p->img_height || (p->band_rows > 0 && p->band_period > 1)) RT_CUDA(ctx, cudaMemsetAsync(ctx->b_pixels.ptr, 0, n * 3 * sizeof(float), ctx->stream));
   rt_stats local;
   rc = rt_render_device(ctx, p, (float *)ctx->b_pixels.ptr, &local);
   if (rc != RT_OK) return rc;

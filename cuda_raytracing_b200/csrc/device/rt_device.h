@@ -95,6 +95,8 @@ struct RenderArgs {
   uint32_t slots_per_chunk;     // 32 * number of 32-pixel tiles covering the rendered rows (>= pixel_count)
   uint32_t tiles_x, tile_shift; // tiles per row of tiles; log2 of the tile width (tile = 2^s x 2^(5-s) pixels)
   int32_t first_row;            // first_pixel / img_width
+  int32_t band_rows, band_period, band_phase;   // band_rows > 0: row y of the rendered set is image row
+                                // ((y / band_rows) * band_period + band_phase) * band_rows + y % band_rows (interleaved bands)
   int32_t chunk_samples, chunk_count;   // a pixel's samples are produced in order, chunk_samples at a time
   int32_t claim_group;          // idle lanes of a warp claim work items together, this many at a time
   int32_t img_width, img_height, samples_per_pixel, max_bounces;

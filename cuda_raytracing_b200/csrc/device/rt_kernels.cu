@@ -65,6 +65,18 @@ __device__ __forceinline__ bool trace(const Scene &sc, Ray &r, Hit &h, uint32_t 
   return rtt::trace_fast(sc, r, 0.001f, inf, h, stk, stride, cnt);
 }
 
+// rendered set -> image: the set is a run of rows, or interleaved bands of rows (tile sharding in one launch)
+__device__ __forceinline__ int image_row(const RenderArgs &a, int y) {
+  if (a.band_rows == 0) return a.first_row + y;
+  const int k = y / a.band_rows;
+  return (k * a.band_period + a.band_phase) * a.band_rows + (y - k * a.band_rows);
+}
+__device__ __forceinline__ size_t image_pixel(const RenderArgs &a, int pix) {
+  if (a.band_rows == 0) return (size_t)a.first_pixel + (size_t)pix;
+  const int y = pix / a.img_width;
+  return (size_t)image_row(a, y) * (size_t)a.img_width + (size_t)(pix - y * a.img_width);
+}
+
 template <int MODE, int MAXB, bool COUNT>
 __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_MIN_BLOCKS_REF) render_kernel(const RenderArgs a) {
   extern __shared__ __align__(16) uint32_t smem[];
@@ -133,7 +145,7 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
           if (x < (uint32_t)a.img_width && y * (uint32_t)a.img_width + x < (uint32_t)a.pixel_count) {
             pix = (int)(y * (uint32_t)a.img_width + x);
             waiting = true;
-            const float fi = (float)(a.first_row + (int)y), fj = (float)x;     // rt.cu:1561-1567
+            const float fi = (float)image_row(a, (int)y), fj = (float)x;     // rt.cu:1561-1567
             base = v3(fadd(ffma(fj, du.x, fmul(fi, dv.x)), a.p00[0]), fadd(ffma(fj, du.y, fmul(fi, dv.y)), a.p00[1]),
                       fadd(ffma(fj, du.z, fmul(fi, dv.z)), a.p00[2]));
           }
@@ -149,8 +161,7 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
       const uint2 *st = reinterpret_cast<const uint2 *>(a.rng_states) + 3 * (size_t)pix;
       const uint2 s0 = __ldcg(st), s1 = __ldcg(st + 1), s2 = __ldcg(st + 2);
       rng.d = s0.x; rng.v0 = s0.y; rng.v1 = s1.x; rng.v2 = s1.y; rng.v3 = s2.x; rng.v4 = s2.y;
-      const int gp = a.first_pixel + pix;
-      float *out = a.pixels + 3 * (size_t)gp;
+      float *out = a.pixels + 3 * image_pixel(a, pix);
       acc = chunk ? v3(__ldcg(out), __ldcg(out + 1), __ldcg(out + 2)) : v3(0.0f, 0.0f, 0.0f);
       const int done = chunk * a.chunk_samples;
       samples_left = a.samples_per_pixel - done < a.chunk_samples ? a.samples_per_pixel - done : a.chunk_samples;
@@ -238,7 +249,7 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
       acc = vadd(acc, result);
       new_path = true;
       if (--samples_left == 0) {                         // chunk done: final value, or running sum + state for the next owner
-        float *out = a.pixels + 3 * ((size_t)a.first_pixel + (size_t)pix);
+        float *out = a.pixels + 3 * image_pixel(a, pix);
         uint2 *st = reinterpret_cast<uint2 *>(a.rng_states + 6 * (size_t)pix);
         const bool last = (chunk + 1 == a.chunk_count);
         __stcg(out, last ? fmul(a.sample_scale, acc.x) : acc.x);

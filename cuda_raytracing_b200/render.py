@@ -8,9 +8,9 @@ Sharding (cuda_raytracing_b200/sharding.py):
   samples  rank g renders its share of the samples of EVERY pixel (XORWOW subsequence = pixel + g * n_pixels, so
            rank 0 carries the reference's stream) into an f32 SUM image; one `reduce(SUM)` onto rank 0; rank 0
            scales by 1/spp, resolves (gamma + 8 bit) and writes the PPM.  Statistical (tier-2) parity.
-  tiles    rank g renders interleaved bands of rows (16 per rank) with the reference's stream (subsequence = pixel); bands are
-           disjoint, so the same `reduce(SUM)` over zero-initialised images assembles the picture exactly
-           (x + 0 == x): bit-identical to the 1-GPU image.
+  tiles    rank g renders interleaved bands of rows (~32 per rank, ONE launch: rt_render_params.band_*) with the
+           reference's stream (subsequence = pixel); bands are disjoint, so the same `reduce(SUM)` over zero-initialised
+           images assembles the picture exactly (x + 0 == x): bit-identical to the 1-GPU image.
 Everything else (scene construction in C, packing, the render kernel) is the single-GPU path of the C ABI.
 Prints the reference's four stdout lines (rt.cu:1759-1768) on rank 0 and one JSON line with the statistics on stderr.
 """
@@ -59,13 +59,17 @@ def parse_args(argv):
     return opts
 
 
+def band_rows(opts, world, height):
+    """Rows per interleaved band of the tile sharding: ~32 bands per rank balance sky against interior."""
+    return opts["band"] or max(4, height // (world * 32))
+
+
 def plan(opts, rank, world, width, height, spp):
-    """What this rank renders: a list of (row_begin, row_end, spp, subsequence_offset) calls and the total spp."""
+    """What this rank renders: a list of (row_begin, row_end, spp, subsequence_offset) and the total spp.  For the tile
+    sharding the list names the rank's bands; main() renders them in ONE launch (rt_render_params.band_*)."""
     from . import sharding
     if opts["shard"] == "tiles" and world > 1:
-        # one kernel launch per band: 16 interleaved bands per rank balance sky against interior at full occupancy
-        band = opts["band"] or max(8, height // (world * 16))
-        return [(a, b, spp, 0) for (a, b) in sharding.tile_rows(rank, world, height, band)], spp
+        return [(a, b, spp, 0) for (a, b) in sharding.tile_rows(rank, world, height, band_rows(opts, world, height))], spp
     off, mine, total = sharding.sample_shard(rank, world, width * height, total_spp=spp)
     return ([(0, height, mine, off)] if mine > 0 else []), total
 
@@ -114,13 +118,19 @@ def main(argv=None):
     e0.record(stream)
     tiles = opts["shard"] == "tiles" and world > 1
     st = None
-    for (r0, r1, my_spp, off) in calls:
-        p = hs.params(opts["width"], my_spp, opts["bounces"], subsequence_offset=off,
-                      flags=rt.RT_RENDER_COUNT_RAYS | (0 if tiles else rt.RT_RENDER_OUTPUT_SUM))
-        p.row_begin, p.row_end = r0, r1
-        st = ctx.render_device(p, pixels.data_ptr(), stats=True)        # stats: ray counter read-back (one sync per band)
-        paths += st.paths
-        rays += st.rays
+    if tiles and calls:                                                  # all of this rank's bands in one launch
+        p = hs.params(opts["width"], spp, opts["bounces"], flags=rt.RT_RENDER_COUNT_RAYS)
+        p.band_rows, p.band_period, p.band_phase = band_rows(opts, world, H), world, rank
+        st = ctx.render_device(p, pixels.data_ptr(), stats=True)
+        paths, rays = st.paths, st.rays
+    elif not tiles:
+        for (r0, r1, my_spp, off) in calls:
+            p = hs.params(opts["width"], my_spp, opts["bounces"], subsequence_offset=off,
+                          flags=rt.RT_RENDER_COUNT_RAYS | rt.RT_RENDER_OUTPUT_SUM)
+            p.row_begin, p.row_end = r0, r1
+            st = ctx.render_device(p, pixels.data_ptr(), stats=True)    # stats: ray counter read-back
+            paths += st.paths
+            rays += st.rays
     e1.record(stream)
     if world > 1:
         dist.reduce(pixels, dst=0, op=dist.ReduceOp.SUM)                 # NCCL over NVLink: the one exchange

@@ -83,7 +83,10 @@ typedef struct rt_render_params {
   uint64_t subsequence_offset;    /* XORWOW subsequence = pixel index + this; 0 = the reference's stream */
   int32_t row_begin, row_end;     /* render rows [row_begin,row_end) only (tile sharding); 0,0 = whole image */
   uint32_t flags;
-  uint32_t reserved;
+  /* interleaved row bands (tile sharding in ONE launch): with band_rows > 0 and band_period > 1 the call renders the
+   * rows r with (r / band_rows) % band_period == band_phase and leaves the others untouched (row_begin/row_end must
+   * be 0,0 or the whole image).  Same stream, same pixels as rendering the bands one by one. */
+  uint32_t band_rows, band_period, band_phase;
 } rt_render_params;
 
 typedef struct rt_stats {

@@ -33,7 +33,7 @@ def test_exports_every_declared_symbol(product_lib):
 
 def test_struct_layouts_match_header(product_lib):
     # sizes the C side asserts too (rt_world.c _Static_asserts); these guard the ctypes mirrors
-    assert C.sizeof(product_lib.api.RenderParams) == 136
+    assert C.sizeof(product_lib.api.RenderParams) == 144
     assert C.sizeof(product_lib.api.ProbeHit) == 72
     assert C.sizeof(product_lib.api.RenderSettings) == 80       # == the reference's RenderSettings
     assert C.sizeof(product_lib.api.SceneDesc) == 56

@@ -357,3 +357,35 @@ def test_hybrid_walk_equals_reference_order(product_lib, sid):
             if a.hit:
                 assert a.t == b.t and list(a.point[:]) == list(b.point[:]) and list(a.normal[:]) == list(b.normal[:]), (sid, i)
     hs.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sid,world,band", [(2, 3, 8), (1, 4, 5), (3, 2, 16)])
+def test_interleaved_row_bands_assemble_the_full_image(gpu_ctx, product_lib, sid, world, band):
+    """Tile sharding in one launch (rt_render_params.band_*): the `world` banded renders touch disjoint rows, leave
+    the others alone, and together are the full render bit for bit (what the NCCL reduce over zero-initialised images
+    assembles).  Height is not a multiple of the band on purpose."""
+    hs = product_lib.HostScene(sid)
+    gpu_ctx.upload(hs, product_lib.RT_TRAVERSAL_AUTO)
+    p = hs.params(90, 5, 10)
+    full, _, _ = gpu_ctx.render(p)
+    total = np.zeros_like(full)
+    paths = 0
+    for rank in range(world):
+        q = hs.params(90, 5, 10)
+        q.band_rows, q.band_period, q.band_phase = band, world, rank
+        img, _, st = gpu_ctx.render(q)
+        rows = [r for r in range(full.shape[0]) if (r // band) % world == rank]
+        others = [r for r in range(full.shape[0]) if (r // band) % world != rank]
+        assert np.array_equal(common.bits(img[rows]), common.bits(full[rows])), (sid, rank)
+        assert not img[others].any()
+        assert st.paths == len(rows) * full.shape[1] * 5
+        total += img
+        paths += st.paths
+    assert np.array_equal(common.bits(total), common.bits(full))
+    assert paths == full.shape[0] * full.shape[1] * 5
+    q = hs.params(90, 5, 10)
+    q.band_rows, q.band_period, q.band_phase = band, world, world              # phase out of range
+    with pytest.raises(product_lib.RtError):
+        gpu_ctx.render(q)
+    hs.close()
