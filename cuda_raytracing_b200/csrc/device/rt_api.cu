@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <algorithm>
 
 #include <chrono>
 #include <string>
@@ -285,6 +286,11 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
     a.claim_group = ctx->claim_group > 0 ? ctx->claim_group : (big_fast ? 32 : 1);
   }
   a.counters = (unsigned long long *)ctx->b_counters.ptr;
+  {   // shared-memory traversal stack: what this scene's walk can need, in multiples of 4 entries (16-byte rows per thread quad)
+    const uint32_t need = ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? ctx->packed.fast_stack_need : ctx->packed.ref_stack_need;
+    a.stack_entries = (int32_t)std::min<uint32_t>((need + 3u) & ~3u, (uint32_t)rtd::STACK_CAPACITY);
+    if (a.stack_entries < 4) a.stack_entries = 4;
+  }
   a.img_width = p->img_width; a.img_height = p->img_height;
   a.samples_per_pixel = p->samples_per_pixel; a.max_bounces = p->max_bounces;
   a.first_pixel = (int32_t)first_pixel; a.pixel_count = (int32_t)count;

@@ -99,6 +99,7 @@ struct RenderArgs {
                                 // ((y / band_rows) * band_period + band_phase) * band_rows + y % band_rows (interleaved bands)
   int32_t chunk_samples, chunk_count;   // a pixel's samples are produced in order, chunk_samples at a time
   int32_t claim_group;          // idle lanes of a warp claim work items together, this many at a time
+  int32_t stack_entries;        // traversal stack entries per thread that this scene needs (<= STACK_CAPACITY): sizes the shared memory
   int32_t img_width, img_height, samples_per_pixel, max_bounces;
   int32_t first_pixel, pixel_count;   // rendered range (row_begin*W .. row_end*W)
   float defocus_angle;

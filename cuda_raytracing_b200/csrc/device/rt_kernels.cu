@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
   PerlinSmem *perlin = nullptr;
   float *coop = nullptr;                                // per-warp scratch of the cooperative turbulence
   if (sc.perlin_tables > 0) {
-    perlin = reinterpret_cast<PerlinSmem *>(smem + rtd::STACK_CAPACITY * blockDim.x);
+    perlin = reinterpret_cast<PerlinSmem *>(smem + a.stack_entries * blockDim.x);
     coop = reinterpret_cast<float *>(perlin + 1) + (threadIdx.x >> 5) * rts::COOP_WORDS_PER_WARP;
     stage_perlin(sc, perlin);
     __syncthreads();
@@ -472,7 +472,7 @@ cudaError_t launch_probe_texture(const rtd::Scene &scene, uint64_t n, uint32_t t
 // ======================================================================================================
 template <int MODE, int MAXB, bool COUNT>
 static cudaError_t launch_render_t(const RenderArgs &args, int sm_count, cudaStream_t stream, LaunchInfo *info) {
-  size_t smem = sizeof(uint32_t) * rtd::STACK_CAPACITY * RT_BLOCK;
+  size_t smem = sizeof(uint32_t) * (size_t)args.stack_entries * RT_BLOCK;
   if (args.scene.perlin_tables > 0) smem += sizeof(PerlinSmem) + sizeof(float) * rts::COOP_WORDS_PER_WARP * (RT_BLOCK / 32);
   auto kernel = render_kernel<MODE, MAXB, COUNT>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
