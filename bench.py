@@ -115,7 +115,7 @@ def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    spp = 2
+    spp = 16                      # a bounded sample per step; the per-pixel XORWOW init of the reference is amortised like in the full run
     for _ in range(args.warmup):
         cpu_reference_render(1)
     paths = secs = 0.0
@@ -297,11 +297,19 @@ def run_gpu_arm(args):
     hbm = {"kernel": "resolve_kernel", "bytes_per_launch": n * 15, "ms": resolve_ms, "achieved_gbs": n * 15 / (resolve_ms / 1e3) / 1e9,
            "peak_gbs": peaks.get("hbm_gbs"), "note": "12 MB working set is L2-resident when timed back to back; HBM is <0.1% of the step by design"}
 
+    traffic = None                                   # DRAM bytes of one launch from the committed ncu capture of this command
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")) as f:
+            tr = json.load(f)
+        if WORKLOAD.startswith(tr.get("workload", "?")):
+            traffic = int(tr["dram_bytes_read"]) + int(tr["dram_bytes_write"])
+    except (OSError, ValueError, KeyError):
+        traffic = None
     cpu = None
     if world == 1:
-        paths, dt, kind, cores = cpu_reference_render(8)
+        paths, dt, kind, cores = cpu_reference_render(16)
         cpu = {"value": paths / dt, "unit": UNIT, "cores": cores, "kind": kind,
-               "sample": "1200x675, b50, s8 (6.48 Mpaths) of the s256 workload, OpenMP over rows, %.1f s wall" % dt}
+               "sample": "1200x675, b50, s16 (12.96 Mpaths) of the s256 workload, OpenMP over rows, %.1f s wall" % dt}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -314,7 +322,7 @@ def run_gpu_arm(args):
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "what": "rt_render_world(): scene H2D + RNG init + render + resolve + f32/rgb8 image D2H"},
         "gpu_launches": 2 * args.steps,
-        "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak, "traffic": None,
+        "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak, "traffic": traffic,
                      "kernel": "render_kernel<fast,64>", "kernel_ms": kernel_ms, "flops_per_ray": f_ray, "rays_per_path": rays_per_path,
                      "mrays_per_s": rays_per_launch / (kernel_ms / 1e3) / 1e6, "per_ray_ops": per_ray, "peak_source": FP32_PEAK_NOTE + "; " + peak_src,
                      "note": "SURVEY.md 8(d): this path is bound by the FP32 pipe / issue rate, not HBM or tensor cores", "hbm": hbm},
