@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "libraytracing_b200.so")   # env: kernel-variant experiments
 
 RT_TRAVERSAL_AUTO, RT_TRAVERSAL_REFERENCE, RT_TRAVERSAL_FAST = 0, 1, 2
-RT_RENDER_OUTPUT_SUM, RT_RENDER_NO_RNG_CACHE, RT_RENDER_COUNT_RAYS, RT_RENDER_COUNT_OPS = 1, 2, 4, 8
+RT_RENDER_OUTPUT_SUM, RT_RENDER_NO_RNG_CACHE, RT_RENDER_COUNT_RAYS, RT_RENDER_COUNT_OPS, RT_RENDER_RESUME = 1, 2, 4, 8, 16
 OP_NAMES = ["box", "sphere", "planar", "translation", "rotation", "lambert", "metal", "glass", "light", "noise", "checker", "arena"]
 
 
@@ -22,6 +22,14 @@ class RtError(RuntimeError):
 
 class Vec3(C.Structure):
     _fields_ = [("x", C.c_float), ("y", C.c_float), ("z", C.c_float)]
+
+
+class Material(C.Structure):  # rt_material (24 B): type, pad, 16-byte union
+    _fields_ = [("type", C.c_uint32), ("pad_", C.c_uint32), ("u", C.c_uint8 * 16)]
+
+
+class Xform(C.Structure):  # rt_xform
+    _fields_ = [("rotate", C.c_int), ("angle_deg", C.c_float), ("translate", C.c_int), ("offset", Vec3)]
 
 
 class World(C.Structure):  # rt_world
@@ -78,9 +86,11 @@ EXPORTS = [
     # rt_api.h
     "rt_context_create", "rt_context_destroy", "rt_last_error_string", "rt_context_set_stream", "rt_context_reset_stream", "rt_scene_upload",
     "rt_render_params_from_camera", "rt_render_device", "rt_resolve_device", "rt_render", "rt_synchronize",
+    "rt_render_state_save", "rt_render_state_load",
     "rt_render_world", "rt_probe_trace", "rt_probe_scatter", "rt_probe_texture", "rt_probe_xorwow",
     # rt_scene.h
     "rt_world_init", "rt_world_free", "rt_mat_lambert_solid", "rt_mat_light_solid", "rt_mat_lambert_image",
+    "rt_mat_lambert_image_pixels",
     "rt_mat_lambert_noise", "rt_mat_lambert_checker", "rt_mat_metal", "rt_mat_dielectric", "rt_add_sphere",
     "rt_add_moving_sphere", "rt_add_quad", "rt_add_triangle", "rt_add_box", "rt_add_pyramid", "rt_host_random",
     "rt_host_random_range", "rt_host_random_int", "rt_world_build_bvh", "rt_world_stack_bound",
@@ -112,6 +122,8 @@ def lib():
         L.rt_resolve_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_float, C.c_void_p]
         L.rt_render.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.POINTER(Stats)]
         L.rt_synchronize.argtypes = [C.c_void_p]
+        L.rt_render_state_save.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+        L.rt_render_state_load.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_uint64]
         L.rt_render_world.argtypes = [C.c_void_p, C.POINTER(World), C.POINTER(RenderSettings), C.c_uint32, C.c_void_p,
                                       C.c_void_p, C.POINTER(Stats)]
         L.rt_probe_trace.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float,
@@ -124,6 +136,12 @@ def lib():
         L.rt_world_free.restype = None
         L.rt_world_build_bvh.argtypes = [C.POINTER(World)]
         L.rt_world_build_bvh.restype = C.c_uint32
+        L.rt_mat_lambert_solid.argtypes = [C.POINTER(World), Vec3]
+        L.rt_mat_lambert_solid.restype = Material
+        L.rt_mat_lambert_image_pixels.argtypes = [C.POINTER(World), C.c_void_p, C.c_int32, C.c_int32]
+        L.rt_mat_lambert_image_pixels.restype = Material
+        L.rt_add_sphere.argtypes = [C.POINTER(World), Xform, Vec3, C.c_float, Material]
+        L.rt_add_sphere.restype = C.c_uint32
         L.rt_world_stack_bound.argtypes = [C.POINTER(World)]
         L.rt_world_stack_bound.restype = C.c_uint64
         L.rt_default_render_settings.argtypes = [C.POINTER(RenderSettings)]
@@ -156,12 +174,30 @@ class HostScene:
             raise MemoryError("rt_world_init")
         L.rt_default_render_settings(C.byref(self.settings))
         L.rt_host_rand_reset()
+        if scene_id is None:                              # an empty world for the add_* / mat_* helpers below
+            self.scene_id = None
+            return
         if L.rt_scene_by_id(scene_id, C.byref(self.world), C.byref(self.settings)) != 0:
             L.rt_world_free(C.byref(self.world))
             raise ValueError("Unknown scene %r" % (scene_id,))
         self.scene_id = scene_id
         if build_bvh:
             L.rt_world_build_bvh(C.byref(self.world))
+
+    # a small part of the C scene-construction surface, for tests that need a world the 20 built-in scenes lack
+    def mat_lambert_solid(self, rgb):
+        return lib().rt_mat_lambert_solid(C.byref(self.world), Vec3(*[float(x) for x in rgb]))
+
+    def mat_lambert_image_pixels(self, pixels):
+        """pixels: float32 [height, width, 3], top row first (what stbi_loadf returns)."""
+        px = np.ascontiguousarray(pixels, dtype=np.float32)
+        return lib().rt_mat_lambert_image_pixels(C.byref(self.world), px.ctypes.data, px.shape[1], px.shape[0])
+
+    def add_sphere(self, center, radius, material):
+        return lib().rt_add_sphere(C.byref(self.world), Xform(), Vec3(*[float(x) for x in center]), float(radius), material)
+
+    def build_bvh(self):
+        return lib().rt_world_build_bvh(C.byref(self.world))
 
     def arrays(self):
         w = self.world
@@ -261,6 +297,18 @@ class Context:
 
     def synchronize(self):
         _check(lib().rt_synchronize(self._h), self._h)
+
+    def save_state(self):
+        """XORWOW states of the last render (uint32[n, 6]) -- with the caller's sum image, all a resume needs."""
+        need = C.c_uint64(0)
+        _check(lib().rt_render_state_save(self._h, None, 0, C.byref(need)), self._h)
+        out = np.empty((need.value // 24, 6), dtype=np.uint32)
+        _check(lib().rt_render_state_save(self._h, out.ctypes.data, out.nbytes, C.byref(need)), self._h)
+        return out
+
+    def load_state(self, params, state):
+        state = np.ascontiguousarray(state, dtype=np.uint32)
+        _check(lib().rt_render_state_load(self._h, C.byref(params), state.ctypes.data, state.nbytes), self._h)
 
     def render_world(self, scene, settings=None, traversal=RT_TRAVERSAL_AUTO):
         """The reference's render(World*, RenderSettings*) in one call."""

@@ -66,7 +66,8 @@ struct rt_context {
   uint32_t fuse_min = 8;                                   // env RT_FUSE_MIN: wrapper chains around one object become one item when there are this many (0 = never)
   uint32_t treelet_min = 8;                                // env RT_TREELET_MIN: smallest wrapper-free subtree given an own BVH (0 = none)
   int tile_w = 8;                                          // work items walk 8x4-pixel tiles; env RT_TILE_W (1..32, power of 2)
-  uint64_t rng_seed = 0, rng_first = 0, rng_count = 0, rng_bands = 0; bool rng_valid = false;
+  uint64_t rng_seed = 0, rng_first = 0, rng_count = 0, rng_bands = 0; bool rng_valid = false;   // what b_rng_init holds
+  uint64_t live_seed = 0, live_first = 0, live_count = 0, live_bands = 0; bool live_valid = false;  // what b_rng_states carries on from
   // scratch for rt_render (host-buffer path)
   DeviceBuffer b_pixels, b_rgb8;
   rtk::LaunchInfo last_launch{};
@@ -197,6 +198,27 @@ static int check_params(rt_context *ctx, const rt_render_params *p, int *row0, i
   return RT_OK;
 }
 
+// the rendered set of a call: a run of rows, or interleaved bands of rows (tile sharding in one launch)
+struct RenderSet { bool banded; uint32_t rows; uint64_t first_pixel, count, first_sub, band_key; };
+static int render_set(rt_context *ctx, const rt_render_params *p, int row0, int row1, RenderSet *out) {
+  out->banded = p->band_rows > 0 && p->band_period > 1;
+  out->rows = (uint32_t)(row1 - row0);
+  if (out->banded) {
+    if (p->band_phase >= p->band_period) return fail(ctx, RT_ERR_INVALID, "rt_render: band_phase must be below band_period");
+    if (row0 != 0 || row1 != p->img_height) return fail(ctx, RT_ERR_INVALID, "rt_render: row bands need the whole row range");
+    out->rows = 0;
+    for (uint64_t b = p->band_phase; b * p->band_rows < (uint64_t)p->img_height; b += p->band_period) {
+      const uint64_t lo = b * p->band_rows, hi = lo + p->band_rows;
+      out->rows += (uint32_t)((hi < (uint64_t)p->img_height ? hi : (uint64_t)p->img_height) - lo);
+    }
+  }
+  out->first_pixel = out->banded ? 0 : (uint64_t)row0 * p->img_width;
+  out->count = (uint64_t)out->rows * p->img_width;
+  out->first_sub = out->first_pixel + p->subsequence_offset;
+  out->band_key = out->banded ? ((uint64_t)p->band_rows << 40) ^ ((uint64_t)p->band_period << 20) ^ p->band_phase ^ (1ull << 63) : 0;
+  return RT_OK;
+}
+
 int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels, rt_stats *stats) {
   int row0, row1;
   int rc = check_params(ctx, p, &row0, &row1);
@@ -204,31 +226,28 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   if (!d_pixels) return fail(ctx, RT_ERR_INVALID, "rt_render_device: d_pixels_rgb is NULL");
   RT_CUDA(ctx, cudaSetDevice(ctx->device));
   cudaStream_t s = ctx->stream;
-  // the rendered set: a run of rows, or interleaved bands of rows (tile sharding in one launch)
-  const bool banded = p->band_rows > 0 && p->band_period > 1;
-  uint32_t set_rows = (uint32_t)(row1 - row0);
-  if (banded) {
-    if (p->band_phase >= p->band_period) return fail(ctx, RT_ERR_INVALID, "rt_render: band_phase must be below band_period");
-    if (row0 != 0 || row1 != p->img_height) return fail(ctx, RT_ERR_INVALID, "rt_render: row bands need the whole row range");
-    set_rows = 0;
-    for (uint64_t b = p->band_phase; b * p->band_rows < (uint64_t)p->img_height; b += p->band_period) {
-      const uint64_t lo = b * p->band_rows, hi = lo + p->band_rows;
-      set_rows += (uint32_t)((hi < (uint64_t)p->img_height ? hi : (uint64_t)p->img_height) - lo);
-    }
-    if (set_rows == 0) {                                   // more ranks than bands: nothing to do for this one
-      if (stats) { memset(stats, 0, sizeof(*stats)); stats->traversal_used = ctx->packed.traversal_used; }
-      return RT_OK;
-    }
+  RenderSet set;
+  rc = render_set(ctx, p, row0, row1, &set);
+  if (rc != RT_OK) return rc;
+  if (set.rows == 0) {                                     // more ranks than bands: nothing to do for this one
+    if (stats) { memset(stats, 0, sizeof(*stats)); stats->traversal_used = ctx->packed.traversal_used; }
+    return RT_OK;
   }
-  const uint64_t first_pixel = banded ? 0 : (uint64_t)row0 * p->img_width, count = (uint64_t)set_rows * p->img_width;
-  const uint64_t first_sub = first_pixel + p->subsequence_offset;
-  const uint64_t band_key = banded ? ((uint64_t)p->band_rows << 40) ^ ((uint64_t)p->band_period << 20) ^ p->band_phase ^ (1ull << 63) : 0;
+  const bool banded = set.banded;
+  const uint32_t set_rows = set.rows;
+  const uint64_t first_pixel = set.first_pixel, count = set.count, first_sub = set.first_sub, band_key = set.band_key;
+  const bool resume = (p->flags & RT_RENDER_RESUME) != 0;
+  if (resume) {
+    if (!(p->flags & RT_RENDER_OUTPUT_SUM)) return fail(ctx, RT_ERR_INVALID, "rt_render: RT_RENDER_RESUME needs RT_RENDER_OUTPUT_SUM (the buffer must hold sums)");
+    if (!(ctx->live_valid && ctx->live_seed == p->seed && ctx->live_first == first_sub && ctx->live_count == count && ctx->live_bands == band_key))
+      return fail(ctx, RT_ERR_INVALID, "rt_render: RT_RENDER_RESUME without a previous render (or loaded state) of the same seed, rows and subsequence offset");
+  }
 
   uint32_t launches = 0;
   if (stats) RT_CUDA(ctx, cudaEventRecord(ctx->ev[0], s));
   const bool cached = ctx->rng_valid && ctx->rng_seed == p->seed && ctx->rng_first == first_sub && ctx->rng_count == count &&
                       ctx->rng_bands == band_key && !(p->flags & RT_RENDER_NO_RNG_CACHE);
-  if (!cached) {
+  if (!cached && !resume) {
     RT_CUDA(ctx, ctx->b_rng_init.reserve(count * 6 * sizeof(uint32_t)));
     if (!banded) {
       RT_CUDA(ctx, rtk::launch_rng_init(p->seed, first_sub, count, (const uint32_t *)ctx->b_rng_mats.ptr,
@@ -249,7 +268,8 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   // the render kernel advances the states chunk by chunk: it works on a copy, the initial states stay cached
   RT_CUDA(ctx, ctx->b_rng_states.reserve(count * 6 * sizeof(uint32_t)));
   RT_CUDA(ctx, ctx->b_progress.reserve(count * sizeof(uint32_t)));
-  RT_CUDA(ctx, cudaMemcpyAsync(ctx->b_rng_states.ptr, ctx->b_rng_init.ptr, count * 6 * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+  if (!resume) RT_CUDA(ctx, cudaMemcpyAsync(ctx->b_rng_states.ptr, ctx->b_rng_init.ptr, count * 6 * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+  ctx->live_seed = p->seed; ctx->live_first = first_sub; ctx->live_count = count; ctx->live_bands = band_key; ctx->live_valid = true;
   RT_CUDA(ctx, cudaMemsetAsync(ctx->b_progress.ptr, 0, count * sizeof(uint32_t), s));
   RT_CUDA(ctx, cudaMemsetAsync(ctx->b_counters.ptr, 0, 16 * sizeof(unsigned long long), s));
   if (stats) RT_CUDA(ctx, cudaEventRecord(ctx->ev[1], s));
@@ -299,6 +319,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   memcpy(a.cam, p->camera_pos, 12); memcpy(a.ddu, p->defocus_disk_u, 12); memcpy(a.ddv, p->defocus_disk_v, 12);
   memcpy(a.p00, p->pixel00, 12);
   a.sample_scale = (p->flags & RT_RENDER_OUTPUT_SUM) ? 1.0f : 1.0f / (float)p->samples_per_pixel;   // rt.cu:1657
+  a.resume = resume ? 1u : 0u;
   a.count_rays = (p->flags & (RT_RENDER_COUNT_RAYS | RT_RENDER_COUNT_OPS)) ? 1u : 0u;
   a.count_ops = (p->flags & RT_RENDER_COUNT_OPS) ? 1u : 0u;
   // kernel variant: 1 = own BVH over the whole scene, 2 = reference order with treelets, 0 = reference order
@@ -330,6 +351,35 @@ int rt_resolve_device(rt_context *ctx, const float *d_pixels, uint64_t n_pixels,
   if (!ctx || !d_pixels || !d_rgb8) return fail(ctx, RT_ERR_INVALID, "rt_resolve_device: NULL argument");
   RT_CUDA(ctx, cudaSetDevice(ctx->device));
   RT_CUDA(ctx, rtk::launch_resolve(d_pixels, n_pixels, scale, d_rgb8, ctx->stream));
+  return RT_OK;
+}
+
+int rt_render_state_save(rt_context *ctx, void *h_state, uint64_t capacity, uint64_t *bytes_out) {
+  if (!ctx) return fail(nullptr, RT_ERR_INVALID, "rt_render_state_save: ctx is NULL");
+  if (!ctx->live_valid) return fail(ctx, RT_ERR_INVALID, "rt_render_state_save: no render to save");
+  const uint64_t bytes = ctx->live_count * 6 * sizeof(uint32_t);
+  if (bytes_out) *bytes_out = bytes;
+  if (!h_state || capacity < bytes) return h_state ? fail(ctx, RT_ERR_INVALID, "rt_render_state_save: buffer too small") : RT_OK;
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  RT_CUDA(ctx, cudaMemcpyAsync(h_state, ctx->b_rng_states.ptr, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return RT_OK;
+}
+
+int rt_render_state_load(rt_context *ctx, const rt_render_params *p, const void *h_state, uint64_t bytes) {
+  int row0, row1;
+  int rc = check_params(ctx, p, &row0, &row1);
+  if (rc != RT_OK) return rc;
+  if (!h_state) return fail(ctx, RT_ERR_INVALID, "rt_render_state_load: state is NULL");
+  RenderSet set;
+  rc = render_set(ctx, p, row0, row1, &set);
+  if (rc != RT_OK) return rc;
+  if (bytes != set.count * 6 * sizeof(uint32_t)) return fail(ctx, RT_ERR_INVALID, "rt_render_state_load: state size does not match the rendered set");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  RT_CUDA(ctx, ctx->b_rng_states.reserve(bytes));
+  RT_CUDA(ctx, cudaMemcpyAsync(ctx->b_rng_states.ptr, h_state, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->live_seed = p->seed; ctx->live_first = set.first_sub; ctx->live_count = set.count; ctx->live_bands = set.band_key; ctx->live_valid = true;
   return RT_OK;
 }
 

@@ -106,6 +106,7 @@ struct RenderArgs {
   float background[3];
   float dv[3], du[3], cam[3], ddu[3], ddv[3], p00[3];
   float sample_scale;           // 1/spp, or 1 with RT_RENDER_OUTPUT_SUM
+  uint32_t resume;               // chunk 0 starts from the sums already in `pixels` (progressive accumulation)
   uint32_t count_rays;
   uint32_t count_ops;            // run the instrumented kernel variant (per-ray operation counts for F_ray)
 };

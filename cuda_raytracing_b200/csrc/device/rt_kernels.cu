@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
       const uint2 s0 = __ldcg(st), s1 = __ldcg(st + 1), s2 = __ldcg(st + 2);
       rng.d = s0.x; rng.v0 = s0.y; rng.v1 = s1.x; rng.v2 = s1.y; rng.v3 = s2.x; rng.v4 = s2.y;
       float *out = a.pixels + 3 * image_pixel(a, pix);
-      acc = chunk ? v3(__ldcg(out), __ldcg(out + 1), __ldcg(out + 2)) : v3(0.0f, 0.0f, 0.0f);
+      acc = (chunk || a.resume) ? v3(__ldcg(out), __ldcg(out + 1), __ldcg(out + 2)) : v3(0.0f, 0.0f, 0.0f);
       const int done = chunk * a.chunk_samples;
       samples_left = a.samples_per_pixel - done < a.chunk_samples ? a.samples_per_pixel - done : a.chunk_samples;
       new_path = true;

@@ -144,6 +144,25 @@ rt_material rt_mat_lambert_image(rt_world *w, const char *file_name) {
   m.u.texture = texture_append(w, &t, NULL, 0);
   return m;
 }
+rt_material rt_mat_lambert_image_pixels(rt_world *w, const float *rgb, int32_t width, int32_t height) {
+  rt_material m = material_zero(RT_MAT_LAMBERTIAN);
+  rt_texture t; memset(&t, 0, sizeof(t));
+  t.type = RT_TEX_IMAGE;
+  /* (height + 1) rows + 1 texel: everything the reference's inclusive clamp can address (rt.cu:349-352) */
+  const uint64_t texels = (width > 0 && height > 0) ? ((uint64_t)height + 1) * (uint64_t)width + 1 : 0;
+  const uint64_t bytes = texels * 3 * sizeof(float);
+  if (!rgb || texels == 0 || w->texture_bytes + sizeof(rt_texture) + bytes > w->texture_cap) {
+    m.u.texture = texture_append(w, &t, NULL, 0);
+    return m;
+  }
+  float *padded = (float *)calloc(texels * 3, sizeof(float));
+  memcpy(padded, rgb, (uint64_t)width * height * 3 * sizeof(float));
+  t.u.image.width = width; t.u.image.height = height;
+  t.u.image.pixels = (void *)(w->texture_arena + w->texture_bytes + sizeof(rt_texture));   /* non-NULL: "decoded" */
+  m.u.texture = texture_append(w, &t, padded, bytes);
+  free(padded);
+  return m;
+}
 static void perlin_permutation(int32_t *arr, int32_t count) {               /* perlin_noise.cpp:48-59 */
   for (int32_t i = 0; i < count; ++i) arr[i] = i;
   for (int32_t i = count - 1; i > 0; --i) {

@@ -68,7 +68,12 @@ enum {
   RT_RENDER_OUTPUT_SUM = 1u,      /* leave the per-pixel SUM over samples (for multi-GPU sample sharding + reduce) */
   RT_RENDER_NO_RNG_CACHE = 2u,    /* recompute the XORWOW states even if cached from the previous call */
   RT_RENDER_COUNT_RAYS = 4u,      /* fill rt_stats.rays (warp-aggregated counter; small cost) */
-  RT_RENDER_COUNT_OPS = 8u        /* instrumented kernel variant: fill rt_stats.ops (never use for timing) */
+  RT_RENDER_COUNT_OPS = 8u,       /* instrumented kernel variant: fill rt_stats.ops (never use for timing) */
+  RT_RENDER_RESUME = 16u          /* progressive accumulation: carry on from the state the previous
+                                     render of the same seed / rows / subsequence offset left behind -- the per-pixel XORWOW
+                                     states where it stopped, and the per-pixel SUMS still in d_pixels_rgb (needs
+                                     RT_RENDER_OUTPUT_SUM on both).  M samples, then N more == M + N samples in one call,
+                                     bit for bit.  The state can go through the host: rt_render_state_save / _load. */
 };
 /* per-render operation totals of the instrumented variant; index names below */
 enum { RT_OP_BOX = 0, RT_OP_SPHERE, RT_OP_PLANAR, RT_OP_TRANSLATION, RT_OP_ROTATION, RT_OP_LAMBERT, RT_OP_METAL, RT_OP_GLASS,
@@ -110,6 +115,11 @@ int rt_resolve_device(rt_context *ctx, const float *d_pixels_rgb, uint64_t n_pix
 /* host buffers: renders, resolves and copies back (h_rgb8 and/or h_pixels_rgb may be NULL) */
 int rt_render(rt_context *ctx, const rt_render_params *p, float *h_pixels_rgb, uint8_t *h_rgb8, rt_stats *stats);
 int rt_synchronize(rt_context *ctx);
+/* checkpoint / resume: the per-pixel XORWOW states of the last render (24 B per rendered pixel; the sums are the
+ * caller's own pixel buffer).  _save: *bytes_out = size needed; copies when capacity suffices.  _load: makes `state`
+ * (saved after a render with the same seed, rows, bands and subsequence offset as `p`) the one RT_RENDER_RESUME picks up. */
+int rt_render_state_save(rt_context *ctx, void *h_state, uint64_t capacity, uint64_t *bytes_out);
+int rt_render_state_load(rt_context *ctx, const rt_render_params *p, const void *h_state, uint64_t bytes);
 
 /* ---- the whole of render(World*, RenderSettings*) in one call (BVH build if needed, camera, upload, render) ---- */
 int rt_render_world(rt_context *ctx, rt_world *world, const rt_render_settings *settings, uint32_t traversal,

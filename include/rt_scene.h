@@ -122,6 +122,12 @@ static const rt_xform RT_XFORM_NONE = {0, 0.0f, 0, {0.0f, 0.0f, 0.0f}};
 rt_material rt_mat_lambert_solid(rt_world *w, rt_vec3 color);
 rt_material rt_mat_light_solid(rt_world *w, rt_vec3 color);
 rt_material rt_mat_lambert_image(rt_world *w, const char *file_name);   /* file never decoded here: NULL pixels => magenta (rt.cu:346-347) */
+/* image texture from DECODED pixels (what stbi_loadf() would have returned: width*height RGB floats, row-major, top row
+ * first): the decoder stays with the caller (stb_image is third party), the fetch with the reference's clamp semantics
+ * -- x in [0,width], y in [0,height] inclusive, rt.cu:343-354 -- is done on the device.  The reference reads one row
+ * and one texel past its allocation at u = 1 or v = 0; here those texels exist and are 0.  NULL / empty / too big for
+ * the arena: returns the missing-file record (magenta). */
+rt_material rt_mat_lambert_image_pixels(rt_world *w, const float *rgb, int32_t width, int32_t height);
 rt_material rt_mat_lambert_noise(rt_world *w, float scale);             /* consumes rand() like make_perlin_noise */
 rt_material rt_mat_lambert_checker(rt_world *w, float scale, rt_vec3 even, rt_vec3 odd);
 rt_material rt_mat_metal(rt_vec3 albedo, float fuzz);

@@ -389,3 +389,92 @@ def test_interleaved_row_bands_assemble_the_full_image(gpu_ctx, product_lib, sid
     with pytest.raises(product_lib.RtError):
         gpu_ctx.render(q)
     hs.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sid,bands", [(2, False), (3, False), (1, True)])
+def test_progressive_accumulation_equals_one_render(product_lib, sid, bands):
+    """7 samples, then 9 more (RT_RENDER_RESUME), then 8 more after the state went through the host
+    into a fresh context, is the 24-sample render bit for bit -- same XORWOW stream, same order of additions."""
+    import torch
+    hs = product_lib.HostScene(sid)
+    SUM = product_lib.RT_RENDER_OUTPUT_SUM
+
+    def params(spp, extra=0):
+        q = hs.params(80, spp, 10, flags=SUM | extra)
+        if bands:
+            q.band_rows, q.band_period, q.band_phase = 6, 2, 1
+        return q
+
+    ctx = product_lib.Context(0)
+    ctx.upload(hs, product_lib.RT_TRAVERSAL_AUTO)
+    p24 = params(24)
+    n = p24.img_width * p24.img_height
+    whole = torch.zeros(n * 3, dtype=torch.float32, device="cuda:0")
+    ctx.render_device(p24, whole.data_ptr())
+    part = torch.zeros(n * 3, dtype=torch.float32, device="cuda:0")
+    ctx.render_device(params(7), part.data_ptr())
+    with pytest.raises(product_lib.RtError):                      # resuming needs the sums
+        ctx.render_device(hs.params(80, 9, 10, flags=product_lib.RT_RENDER_RESUME), part.data_ptr())
+    st = ctx.render_device(params(9, product_lib.RT_RENDER_RESUME), part.data_ptr())
+    assert st.kernel_launches == 1                                # no XORWOW init, just the render
+    state = ctx.save_state()
+    assert state.shape == (st.paths // 9, 6)
+    sums = part.cpu()
+    ctx.close()
+
+    ctx2 = product_lib.Context(0)
+    ctx2.upload(hs, product_lib.RT_TRAVERSAL_AUTO)
+    with pytest.raises(product_lib.RtError):                      # nothing to resume yet in this context
+        ctx2.render_device(params(8, product_lib.RT_RENDER_RESUME), part.data_ptr())
+    ctx2.load_state(params(8), state)
+    again = sums.to("cuda:0")
+    ctx2.render_device(params(8, product_lib.RT_RENDER_RESUME), again.data_ptr())
+    assert np.array_equal(common.bits(again.cpu().numpy()), common.bits(whole.cpu().numpy()))
+    with pytest.raises(product_lib.RtError):                      # a state of the wrong size is refused
+        ctx2.load_state(params(8), state[:-1])
+    ctx2.close()
+    hs.close()
+
+
+@pytest.mark.gpu
+def test_image_texture_from_decoded_pixels(gpu_ctx, oracle, product_lib):
+    """an image texture whose pixels the caller decoded (rt_mat_lambert_image_pixels) is fetched on
+    the device with the reference's clamp semantics (inclusive upper clamp, Q19) -- probes against the oracle's
+    restatement of image_texture_get_pixel (rt.cu:343-354), and a render against the oracle's render, bit for bit."""
+    rng = np.random.default_rng(77)
+    tex = rng.random((5, 7, 3), dtype=np.float32)
+    hs = product_lib.HostScene(None)
+    mat = hs.mat_lambert_image_pixels(tex)
+    hs.add_sphere((0, 0, -1), 0.5, mat)
+    hs.add_sphere((0, -100.5, -1), 100.0, hs.mat_lambert_solid((0.8, 0.8, 0.0)))
+    hs.build_bvh()
+    hs.settings.img_width = 64; hs.settings.samples_per_pixel = 4; hs.settings.max_bounces = 6
+    hs.settings.lookfrom = product_lib.api.Vec3(0, 0, 1); hs.settings.lookat = product_lib.api.Vec3(0, 0, -1)
+    h, r, t = hs.arrays()
+    off = int(h[0, 48:56].copy().view(np.uint64)[0])                     # sphere 0: material at +40, its texture offset at +48
+    sc = common.oracle_scene(oracle, hs)
+    L = oracle.lib()
+    L.orc_set_fma_profile(1)
+    try:
+        gpu_ctx.upload(hs, product_lib.RT_TRAVERSAL_AUTO)
+        uv = rng.random((512, 2), dtype=np.float32)
+        uv[:8] = [[0, 0], [1, 1], [1, 0], [0, 1], [0.999999, 0.5], [0.5, 1e-7], [1.5, -0.5], [-2, 3]]   # edges and beyond
+        pts = np.zeros((512, 3), dtype=np.float32)
+        got = gpu_ctx.probe_texture(off, uv, pts)
+        want = np.zeros_like(got)
+        for i in range(len(uv)):
+            L.orc_texture_color(C.byref(sc.c), off, float(uv[i, 0]), float(uv[i, 1]), oracle.fptr(pts[i].copy()), oracle.fptr(want[i]))
+        assert np.array_equal(common.bits(got), common.bits(want))
+        assert got[8:].min() >= 0.0 and np.unique(got[8:], axis=0).shape[0] > 20      # really the image, not one colour
+        p = hs.params(0, 0, 0)
+        img, _, _ = gpu_ctx.render(p)
+        cam = common.oracle_camera(oracle, p)
+        ref, _ = oracle.render(sc, cam, gpu_profile=True)
+        L.orc_set_fma_profile(1)
+        # the sphere's (u, v) come from acosf / atan2f (CUDA libm vs glibc: a texel can flip at a boundary), nothing else differs
+        same = (common.bits(img) == common.bits(ref)).all(axis=2).mean()
+        assert same >= 0.99, same
+    finally:
+        L.orc_set_fma_profile(0)
+    hs.close()
