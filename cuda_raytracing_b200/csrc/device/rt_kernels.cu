@@ -82,11 +82,11 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
   extern __shared__ __align__(16) uint32_t smem[];
   const Scene &sc = a.scene;
   uint32_t *stk = smem + threadIdx.x;
-  const int stride = blockDim.x;
+  constexpr int stride = RT_BLOCK;                       // launch_render_t always launches RT_BLOCK threads
   PerlinSmem *perlin = nullptr;
   float *coop = nullptr;                                // per-warp scratch of the cooperative turbulence
   if (sc.perlin_tables > 0) {
-    perlin = reinterpret_cast<PerlinSmem *>(smem + a.stack_entries * blockDim.x);
+    perlin = reinterpret_cast<PerlinSmem *>(smem + a.stack_entries * RT_BLOCK);
     coop = reinterpret_cast<float *>(perlin + 1) + (threadIdx.x >> 5) * rts::COOP_WORDS_PER_WARP;
     stage_perlin(sc, perlin);
     __syncthreads();
