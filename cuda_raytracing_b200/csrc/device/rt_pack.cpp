@@ -468,8 +468,10 @@ struct Packer {
         out.xforms[idx] = f4(h.u.y_rotation.sin_theta, h.u.y_rotation.cos_theta, 0.0f, as_float(tag[h.u.y_rotation.child]));
       } else if (h.type == RT_OBJ_STRUCTURE) {
         if ((uint64_t)h.u.structure.first + h.u.structure.count > n) { out.error = "rt_scene_upload: structure out of range"; return RT_ERR_INVALID; }
+        // each structure's children start on a 16-byte boundary and are padded to whole uint4s (the walk loads 4 at a time)
         uint2 s; s.x = (uint32_t)out.struct_children.size(); s.y = (uint32_t)h.u.structure.count;
         for (uint32_t k = 0; k < s.y; ++k) out.struct_children.push_back(tag[h.u.structure.first + k]);
+        while (out.struct_children.size() & 3u) out.struct_children.push_back(make_ref(K_NONE, 0));
         out.structures[idx] = s;
       }
     }

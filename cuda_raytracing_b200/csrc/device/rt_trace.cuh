@@ -269,9 +269,16 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
         inv.x = frcp(r.d.x); inv.z = frcp(r.d.z);
         a = dot_xfirst(r.d, r.d);
       } break;
-      case rtd::K_STRUCTURE: {
+      case rtd::K_STRUCTURE: {                            // children in slots of 4 (packer pads): one 128-bit load per 4
         const uint2 s = __ldg(sc.structures + idx);
-        for (uint32_t i = 0; i < s.y; ++i) stk[(sp++) * stride] = __ldg(sc.struct_children + s.x + i);
+        const uint4 *kids = reinterpret_cast<const uint4 *>(sc.struct_children + s.x);
+        for (uint32_t i = 0; i < s.y; i += 4) {
+          const uint4 c = __ldg(kids + (i >> 2));
+          stk[(sp++) * stride] = c.x;
+          if (i + 1 < s.y) stk[(sp++) * stride] = c.y;
+          if (i + 2 < s.y) stk[(sp++) * stride] = c.z;
+          if (i + 3 < s.y) stk[(sp++) * stride] = c.w;
+        }
       } break;
       default: {                                            // K_NONE: index 0 = nothing, else node (index - 1) of a treelet
         if (!TREELETS || idx == 0) break;
@@ -301,7 +308,14 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
               was_last_hit = false;
               in_translation = (fl & rtd::INST_TRANSLATE) != 0; in_rotation = (fl & rtd::INST_ROTATE) != 0;
               stk[(sp++) * stride] = cur;
-              for (uint32_t i = 0; i < st.y; ++i) stk[(sp++) * stride] = __ldg(sc.struct_children + st.x + i);
+              const uint4 *kids = reinterpret_cast<const uint4 *>(sc.struct_children + st.x);
+              for (uint32_t i = 0; i < st.y; i += 4) {
+                const uint4 c = __ldg(kids + (i >> 2));
+                stk[(sp++) * stride] = c.x;
+                if (i + 1 < st.y) stk[(sp++) * stride] = c.y;
+                if (i + 2 < st.y) stk[(sp++) * stride] = c.z;
+                if (i + 3 < st.y) stk[(sp++) * stride] = c.w;
+              }
               break;
             }
             if (ck == rtd::K_SPHERE) { cnt.sphere(); hit_in = hit_sphere(sc, ci, r, a, tmin, tmax, h); }
