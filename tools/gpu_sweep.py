@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Sweep the chunk size (env RT_CHUNK, 0 = automatic) on BASELINE configs; RT_B200_LIB selects a library variant
-(tools/build_variants.sh).  usage: gpu_sweep.py CONFIG[:spp] ... -- chunk[,claim_group[,tile_w]] ...   (0 = automatic)
+(tools/build_variants.sh); SWEEP_WIDTH / SWEEP_TRAVERSAL override the image width / traversal.  usage: gpu_sweep.py CONFIG[:spp] ... -- chunk[,claim_group[,tile_w]] ...   (0 = automatic)
 Prints one JSON line per run; the image must not depend on the knobs."""
 import hashlib
 import json
@@ -33,7 +33,7 @@ def main():
             ctx = rt.Context(0)
             hs = rt.HostScene(scene)
             ctx.upload(hs, trav)
-            p = hs.params(0, spp, b)
+            p = hs.params(int(os.environ.get("SWEEP_WIDTH", "0")), spp, b)
             ms = []
             for _ in range(3):
                 img, _, st = ctx.render(p, want_rgb8=False)
