@@ -76,6 +76,12 @@ class Stats(C.Structure):  # rt_stats
                 ("regs_per_thread", C.c_uint32), ("blocks_per_sm", C.c_uint32), ("ops", C.c_uint64 * 12)]
 
 
+class PackInfo(C.Structure):  # rt_pack_info
+    _fields_ = [(n, C.c_uint32) for n in ("traversal_used", "kernel_mode", "spheres", "planars", "own_nodes", "treelets",
+                                          "treelet_prims", "fused_instances", "stack_need", "stack_capacity", "perlin_tables",
+                                          "has_wrappers")]
+
+
 class ProbeHit(C.Structure):  # rt_probe_hit
     _fields_ = [("origin", C.c_float * 3), ("direction", C.c_float * 3), ("point", C.c_float * 3),
                 ("normal", C.c_float * 3), ("t", C.c_float), ("u", C.c_float), ("v", C.c_float),
@@ -87,7 +93,7 @@ EXPORTS = [
     "rt_context_create", "rt_context_destroy", "rt_last_error_string", "rt_context_set_stream", "rt_context_reset_stream", "rt_scene_upload",
     "rt_render_params_from_camera", "rt_render_device", "rt_resolve_device", "rt_render", "rt_synchronize",
     "rt_render_state_save", "rt_render_state_load",
-    "rt_render_world", "rt_probe_trace", "rt_probe_scatter", "rt_probe_texture", "rt_probe_xorwow",
+    "rt_scene_pack_info", "rt_render_world", "rt_probe_trace", "rt_probe_scatter", "rt_probe_texture", "rt_probe_xorwow",
     # rt_scene.h
     "rt_world_init", "rt_world_free", "rt_mat_lambert_solid", "rt_mat_light_solid", "rt_mat_lambert_image",
     "rt_mat_lambert_image_pixels",
@@ -122,6 +128,7 @@ def lib():
         L.rt_resolve_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_float, C.c_void_p]
         L.rt_render.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.POINTER(Stats)]
         L.rt_synchronize.argtypes = [C.c_void_p]
+        L.rt_scene_pack_info.argtypes = [C.POINTER(SceneDesc), C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(PackInfo)]
         L.rt_render_state_save.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.rt_render_state_load.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_uint64]
         L.rt_render_world.argtypes = [C.c_void_p, C.POINTER(World), C.POINTER(RenderSettings), C.c_uint32, C.c_void_p,
@@ -233,6 +240,15 @@ class HostScene:
         p.subsequence_offset = subsequence_offset
         p.flags = flags
         return p
+
+    def pack_info(self, traversal=RT_TRAVERSAL_AUTO, treelet_min=8, fuse_min=8):
+        """What rt_scene_upload would build (host only, no GPU needed)."""
+        info = PackInfo()
+        d = self.desc()
+        rc = lib().rt_scene_pack_info(C.byref(d), traversal, treelet_min, fuse_min, C.byref(info))
+        if rc != 0:
+            raise RtError("rt_scene_pack_info: %d %s" % (rc, (lib().rt_last_error_string(None) or b"").decode()))
+        return info
 
     def close(self):
         if self.world.hittables:

@@ -496,6 +496,23 @@ int rt_probe_texture(rt_context *ctx, uint64_t n, uint64_t texture_offset, const
   return RT_OK;
 }
 
+int rt_scene_pack_info(const rt_scene_desc *scene, uint32_t traversal, uint32_t treelet_min, uint32_t fuse_min, rt_pack_info *out) {
+  if (!scene || !out) return fail(nullptr, RT_ERR_INVALID, "rt_scene_pack_info: NULL argument");
+  rtp::PackedScene p;
+  const int rc = rtp::pack_scene(*scene, traversal, p, treelet_min, fuse_min);
+  if (rc != RT_OK) return fail(nullptr, rc, p.error);
+  memset(out, 0, sizeof(*out));
+  out->traversal_used = p.traversal_used;
+  out->kernel_mode = p.traversal_used == RT_TRAVERSAL_FAST ? 1u : (p.treelets + p.fused_instances > 0 ? 2u : 0u);
+  out->spheres = p.sphere_count; out->planars = p.planar_count;
+  out->own_nodes = (uint32_t)(p.fast_nodes.size() / 4);
+  out->treelets = p.treelets; out->treelet_prims = p.treelet_prims; out->fused_instances = p.fused_instances;
+  out->stack_need = p.traversal_used == RT_TRAVERSAL_FAST ? p.fast_stack_need : p.ref_stack_need;
+  out->stack_capacity = (uint32_t)rtd::STACK_CAPACITY;
+  out->perlin_tables = p.perlin_tables; out->has_wrappers = p.has_wrappers ? 1u : 0u;
+  return RT_OK;
+}
+
 int rt_probe_xorwow(rt_context *ctx, uint64_t seed, uint64_t first_subsequence, uint64_t n, uint32_t *states6_out) {
   if (!ctx || !states6_out) return fail(ctx, RT_ERR_INVALID, "rt_probe_xorwow: NULL argument");
   RT_CUDA(ctx, cudaSetDevice(ctx->device));

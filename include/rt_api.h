@@ -139,6 +139,20 @@ int rt_probe_scatter(rt_context *ctx, uint64_t n, const uint32_t *material6, con
 int rt_probe_texture(rt_context *ctx, uint64_t n, uint64_t texture_offset, const float *uv, const float *points, float *rgb_out);
 int rt_probe_xorwow(rt_context *ctx, uint64_t seed, uint64_t first_subsequence, uint64_t n, uint32_t *states6_out);
 
+/* what rt_scene_upload would build for this scene -- host only, no CUDA call, no context (works without a GPU):
+ * the walk it would use and the sizes of the device structures.  treelet_min / fuse_min as in the RT_TREELET_MIN /
+ * RT_FUSE_MIN knobs (8 / 8 by default). */
+typedef struct rt_pack_info {
+  uint32_t traversal_used;                 /* RT_TRAVERSAL_REFERENCE or RT_TRAVERSAL_FAST */
+  uint32_t kernel_mode;                    /* 0 reference order, 1 own BVH, 2 reference order + treelets / fused instances */
+  uint32_t spheres, planars;               /* primitive records (flattened instances included in FAST mode) */
+  uint32_t own_nodes;                      /* 64-byte own-BVH nodes (whole scene, or all treelets) */
+  uint32_t treelets, treelet_prims, fused_instances;
+  uint32_t stack_need, stack_capacity;     /* traversal stack entries per thread */
+  uint32_t perlin_tables, has_wrappers;
+} rt_pack_info;
+int rt_scene_pack_info(const rt_scene_desc *scene, uint32_t traversal, uint32_t treelet_min, uint32_t fuse_min, rt_pack_info *out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,57 @@
+"""Host logic of the packer (no GPU): which walk a scene gets, what the treelet / fused-instance planting finds, and
+that every built-in scene fits the device limits in every traversal mode (rt_scene_pack_info, host only)."""
+import pytest
+
+
+@pytest.mark.parametrize("sid", list(range(20)))
+def test_every_scene_packs_in_every_mode(product_lib, sid):
+    hs = product_lib.HostScene(sid)
+    for trav in (product_lib.RT_TRAVERSAL_AUTO, product_lib.RT_TRAVERSAL_REFERENCE, product_lib.RT_TRAVERSAL_FAST):
+        i = hs.pack_info(trav)
+        assert 1 <= i.stack_need <= i.stack_capacity
+        assert i.spheres + i.planars >= 1
+        if trav == product_lib.RT_TRAVERSAL_FAST:
+            assert (i.traversal_used, i.kernel_mode) == (product_lib.RT_TRAVERSAL_FAST, 1) and i.own_nodes >= 1
+        if trav == product_lib.RT_TRAVERSAL_REFERENCE:          # the literal walk: no stand-ins
+            assert (i.traversal_used, i.kernel_mode) == (product_lib.RT_TRAVERSAL_REFERENCE, 0)
+            assert i.treelets == i.fused_instances == i.own_nodes == 0
+        if trav == product_lib.RT_TRAVERSAL_AUTO:               # exact results: own BVH only where order cannot matter
+            assert i.traversal_used == (product_lib.RT_TRAVERSAL_REFERENCE if i.has_wrappers else product_lib.RT_TRAVERSAL_FAST)
+    hs.close()
+
+
+def test_final_scene_gets_treelets_and_fused_instances(product_lib):
+    """Scene 3: 400 ground boxes (2400 quads) + light + 5 spheres at top level, 1000 spheres each in translate(rotate())."""
+    hs = product_lib.HostScene(3)
+    i = hs.pack_info()
+    assert (i.traversal_used, i.kernel_mode) == (product_lib.RT_TRAVERSAL_REFERENCE, 2)
+    assert (i.spheres, i.planars) == (1005, 2401)
+    assert i.fused_instances == 1000
+    assert i.treelets == 3 and i.treelet_prims == 2395          # the three wrapper-free subtrees with >= 8 primitives
+    assert i.own_nodes == i.treelet_prims - i.treelets          # a binary tree over n leaves has n - 1 inner nodes
+    off = hs.pack_info(treelet_min=0, fuse_min=0)
+    assert off.kernel_mode == 0 and off.treelets == 0 and off.fused_instances == 0 and off.own_nodes == 0
+    small = hs.pack_info(treelet_min=2)                         # smaller subtrees qualify too: more treelets, more primitives
+    assert small.treelets > i.treelets and small.treelet_prims > i.treelet_prims
+    fast = hs.pack_info(product_lib.RT_TRAVERSAL_FAST)          # instances flattened to world space: 1000 more sphere records
+    assert fast.spheres == 2005 and fast.own_nodes == 2401 + 5 + 1000 - 1   # one leaf per primitive in world space
+    hs.close()
+
+
+def test_small_instance_counts_keep_the_plain_walk(product_lib):
+    """Cornell box: two instances, no wrapper-free subtree of 8 primitives -> plain reference-order kernel (measured
+    faster); the knobs can force the hybrid walk (the GPU parity test does)."""
+    hs = product_lib.HostScene(1)
+    i = hs.pack_info()
+    assert (i.kernel_mode, i.treelets, i.fused_instances) == (0, 0, 0)
+    forced = hs.pack_info(treelet_min=2, fuse_min=1)
+    assert forced.kernel_mode == 2 and forced.fused_instances == 2 and forced.treelets >= 1
+    assert forced.stack_need <= forced.stack_capacity
+    hs.close()
+
+
+def test_pack_info_rejects_bad_input(product_lib):
+    hs = product_lib.HostScene(2)
+    with pytest.raises(product_lib.RtError):
+        hs.pack_info(traversal=7)
+    hs.close()
