@@ -13,6 +13,7 @@
 // attenuation stack in thread-local memory, the accumulator in registers (one 12-byte store per pixel instead
 // of the reference's global read-modify-write per sample).
 #include "rt_kernels.h"
+#include <stdlib.h>
 
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -477,7 +478,18 @@ static cudaError_t launch_render_t(const RenderArgs &args, int sm_count, cudaStr
   auto kernel = render_kernel<MODE, MAXB, COUNT>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, 50);
+  // shared memory carve-out: what the resident blocks need (the scene data and the attenuation stacks live in L1, so
+  // everything else stays cache); env RT_CARVEOUT = percent overrides (tuning knob)
+  int carve = 50;
+  {
+    constexpr int want_blocks = MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_MIN_BLOCKS_REF;
+    const size_t need = (size_t)want_blocks * (smem + 1024 + 1024);     // + static + the per-block reservation
+    carve = (int)((need * 100 + 228 * 1024 - 1) / (228 * 1024)) + 3;
+    if (carve > 100) carve = 100;
+    const char *env = getenv("RT_CARVEOUT");
+    if (env) { const long x = strtol(env, nullptr, 10); if (x >= 0 && x <= 100) carve = (int)x; }
+  }
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve);
   if (e != cudaSuccess) return e;
   int per_sm = 0;
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, RT_BLOCK, smem);
