@@ -180,6 +180,11 @@ int rt_scene_upload(rt_context *ctx, const rt_scene_desc *desc, uint32_t travers
   sc.materials = (const uint4 *)ctx->b_materials.ptr; sc.checkers = (const float4 *)ctx->b_checkers.ptr;
   sc.perlin_vectors = (const float4 *)ctx->b_perlin_vec.ptr; sc.perlin_perm = (const uint8_t *)ctx->b_perlin_perm.ptr;
   sc.perlin_tables = p.perlin_tables; sc.tex_arena = (const uint8_t *)ctx->b_arena.ptr; sc.tex_bytes = p.tex_arena.size();
+  {   // shared-memory traversal stack: what this scene's walk can need, in multiples of 4 entries
+    const uint32_t need = p.traversal_used == RT_TRAVERSAL_FAST ? p.fast_stack_need : p.ref_stack_need;
+    sc.stack_entries = std::min<uint32_t>((need + 3u) & ~3u, (uint32_t)rtd::STACK_CAPACITY);
+    if (sc.stack_entries < 4) sc.stack_entries = 4;
+  }
   ctx->has_scene = true;
   return RT_OK;
 }
@@ -309,11 +314,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
     a.claim_group = ctx->claim_group > 0 ? ctx->claim_group : (big_fast ? 32 : 1);
   }
   a.counters = (unsigned long long *)ctx->b_counters.ptr;
-  {   // shared-memory traversal stack: what this scene's walk can need, in multiples of 4 entries (16-byte rows per thread quad)
-    const uint32_t need = ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? ctx->packed.fast_stack_need : ctx->packed.ref_stack_need;
-    a.stack_entries = (int32_t)std::min<uint32_t>((need + 3u) & ~3u, (uint32_t)rtd::STACK_CAPACITY);
-    if (a.stack_entries < 4) a.stack_entries = 4;
-  }
+  a.stack_entries = (int32_t)ctx->scene.stack_entries;
   a.img_width = p->img_width; a.img_height = p->img_height;
   a.samples_per_pixel = p->samples_per_pixel; a.max_bounces = p->max_bounces;
   a.first_pixel = (int32_t)first_pixel; a.pixel_count = (int32_t)count;

@@ -65,6 +65,7 @@ struct Scene {
   const uint32_t *struct_children;
   const float4 *instances;      // 2 per fused instance: {offset.xyz, child ref} {sin, cos, INST_* flags, 0}
   uint32_t ref_root;            // tagged ref of the reference's root BVH node
+  uint32_t stack_entries;       // traversal stack entries per thread this scene's walk can need (<= STACK_CAPACITY)
   // own BVH over world-space primitives (RT_TRAVERSAL_FAST): 4 x float4 per node
   //   n0 = {c0.x0, c0.x1, c0.y0, c0.y1}  n1 = {c1.x0, c1.x1, c1.y0, c1.y1}
   //   n2 = {c0.z0, c0.z1, c1.z0, c1.z1}  n3 = {child0 ref, child1 ref, 0, 0}

@@ -8,6 +8,14 @@
 #include "rt_device.h"
 #include "rt_math.cuh"
 
+// a push onto the per-thread traversal stack; -DRT_STACK_CHECK builds trap when a walk needs more entries than the packer
+// computed for the scene (tools/build_variants.sh stackcheck "-DRT_STACK_CHECK", then the GPU tests with RT_B200_LIB)
+#ifdef RT_STACK_CHECK
+#define RT_PUSH(v) do { if (sp >= (int)sc.stack_entries) __trap(); stk[(sp++) * stride] = (v); } while (0)
+#else
+#define RT_PUSH(v) (stk[(sp++) * stride] = (v))
+#endif
+
 namespace rtt {
 using namespace rtm;
 using rtd::Scene;
@@ -221,8 +229,8 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
         cnt.box(1);
         if (aabb_axis(n0.x, n0.y, r.o.x, inv.x, t0, t1) && aabb_axis(n0.z, n0.w, r.o.y, inv.y, t0, t1) &&
             aabb_axis(n1.x, n1.y, r.o.z, inv.z, t0, t1)) {
-          stk[(sp++) * stride] = __float_as_uint(n1.w);    // right first => left is visited first (Q11)
-          stk[(sp++) * stride] = __float_as_uint(n1.z);
+          RT_PUSH(__float_as_uint(n1.w));    // right first => left is visited first (Q11)
+          RT_PUSH(__float_as_uint(n1.z));
         }
       } break;
       case rtd::K_TRANSLATION: {
@@ -233,8 +241,8 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
         if (!in_translation) {
           was_last_hit = false;
           r.o = vsub(r.o, off);
-          stk[(sp++) * stride] = cur;                       // comes back as the undo
-          stk[(sp++) * stride] = __float_as_uint(x.w);
+          RT_PUSH(cur);                       // comes back as the undo
+          RT_PUSH(__float_as_uint(x.w));
           in_translation = true;
         } else {
           r.o = vadd(r.o, off);
@@ -252,8 +260,8 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
           const V3 o = r.o, d = r.d;
           r.o = v3(ffma(o.x, cs, -fmul(o.z, sn)), o.y, ffma(o.x, sn, fmul(o.z, cs)));
           r.d = v3(ffma(d.x, cs, -fmul(d.z, sn)), d.y, ffma(d.z, cs, fmul(d.x, sn)));
-          stk[(sp++) * stride] = cur;
-          stk[(sp++) * stride] = __float_as_uint(x.w);
+          RT_PUSH(cur);
+          RT_PUSH(__float_as_uint(x.w));
           in_rotation = true;
         } else {                                            // rt.cu:1210-1236
           const V3 o = r.o, d = r.d;
@@ -274,10 +282,10 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
         const uint4 *kids = reinterpret_cast<const uint4 *>(sc.struct_children + s.x);
         for (uint32_t i = 0; i < s.y; i += 4) {
           const uint4 c = __ldg(kids + (i >> 2));
-          stk[(sp++) * stride] = c.x;
-          if (i + 1 < s.y) stk[(sp++) * stride] = c.y;
-          if (i + 2 < s.y) stk[(sp++) * stride] = c.z;
-          if (i + 3 < s.y) stk[(sp++) * stride] = c.w;
+          RT_PUSH(c.x);
+          if (i + 1 < s.y) RT_PUSH(c.y);
+          if (i + 2 < s.y) RT_PUSH(c.z);
+          if (i + 3 < s.y) RT_PUSH(c.w);
         }
       } break;
       default: {                                            // K_NONE: index 0 = nothing, else node (index - 1) of a treelet
@@ -307,14 +315,14 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
               const uint2 st = __ldg(sc.structures + ci);
               was_last_hit = false;
               in_translation = (fl & rtd::INST_TRANSLATE) != 0; in_rotation = (fl & rtd::INST_ROTATE) != 0;
-              stk[(sp++) * stride] = cur;
+              RT_PUSH(cur);
               const uint4 *kids = reinterpret_cast<const uint4 *>(sc.struct_children + st.x);
               for (uint32_t i = 0; i < st.y; i += 4) {
                 const uint4 c = __ldg(kids + (i >> 2));
-                stk[(sp++) * stride] = c.x;
-                if (i + 1 < st.y) stk[(sp++) * stride] = c.y;
-                if (i + 2 < st.y) stk[(sp++) * stride] = c.z;
-                if (i + 3 < st.y) stk[(sp++) * stride] = c.w;
+                RT_PUSH(c.x);
+                if (i + 1 < st.y) RT_PUSH(c.y);
+                if (i + 2 < st.y) RT_PUSH(c.z);
+                if (i + 3 < st.y) RT_PUSH(c.w);
               }
               break;
             }
@@ -362,10 +370,10 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
         const uint32_t r0 = __float_as_uint(n3.x), r1 = __float_as_uint(n3.y);
         const bool swap = e1 < e0;                          // near child on top
         if (h0 && h1) {
-          stk[(sp++) * stride] = swap ? r0 : r1;
-          stk[(sp++) * stride] = swap ? r1 : r0;
+          RT_PUSH(swap ? r0 : r1);
+          RT_PUSH(swap ? r1 : r0);
         } else if (h0 || h1) {
-          stk[(sp++) * stride] = h0 ? r0 : r1;
+          RT_PUSH(h0 ? r0 : r1);
         }
       } break;
     }
@@ -406,7 +414,7 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
       if (h0 && h1) {
         const bool swap = e1 < e0;
         cur = swap ? r1 : r0;
-        stk[(sp++) * stride] = swap ? r0 : r1;
+        RT_PUSH(swap ? r0 : r1);
         continue;
       } else if (h0 || h1) {
         cur = h0 ? r0 : r1;
