@@ -297,14 +297,16 @@ def run_gpu_arm(args):
     hbm = {"kernel": "resolve_kernel", "bytes_per_launch": n * 15, "ms": resolve_ms, "achieved_gbs": n * 15 / (resolve_ms / 1e3) / 1e9,
            "peak_gbs": peaks.get("hbm_gbs"), "note": "12 MB working set is L2-resident when timed back to back; HBM is <0.1% of the step by design"}
 
-    traffic = None                                   # DRAM bytes of one launch from the committed ncu capture of this command
+    traffic, ncu_note = None, None                   # DRAM bytes of one launch etc. from the committed ncu capture of this command
     try:
         with open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")) as f:
             tr = json.load(f)
         if WORKLOAD.startswith(tr.get("workload", "?")):
             traffic = int(tr["dram_bytes_read"]) + int(tr["dram_bytes_write"])
+            ncu_note = {k: tr[k] for k in ("issue_slot_frac", "lanes_per_warp_instruction", "warp_instructions_per_ray", "l1_hit_pct",
+                                            "l2_hit_pct", "fma_pipe_pct", "source") if k in tr}
     except (OSError, ValueError, KeyError):
-        traffic = None
+        traffic, ncu_note = None, None
     cpu = None
     if world == 1:
         paths, dt, kind, cores = cpu_reference_render(16)
@@ -325,7 +327,8 @@ def run_gpu_arm(args):
         "roofline": {"bound": "fp32", "achieved": achieved, "peak": fp32_peak, "unit": "TFLOP/s", "frac": achieved / fp32_peak, "traffic": traffic,
                      "kernel": "render_kernel<fast,64>", "kernel_ms": kernel_ms, "flops_per_ray": f_ray, "rays_per_path": rays_per_path,
                      "mrays_per_s": rays_per_launch / (kernel_ms / 1e3) / 1e6, "per_ray_ops": per_ray, "peak_source": FP32_PEAK_NOTE + "; " + peak_src,
-                     "note": "SURVEY.md 8(d): this path is bound by the FP32 pipe / issue rate, not HBM or tensor cores", "hbm": hbm},
+                     "note": "SURVEY.md 8(d): this path is bound by the FP32 pipe / issue rate, not HBM or tensor cores", "hbm": hbm,
+                     "ncu": ncu_note},
         "cpu_baseline": cpu,
     }
     if world == 1 and not args.no_reference_gpu:
