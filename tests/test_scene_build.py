@@ -64,3 +64,43 @@ def test_unknown_scene(product_lib):
         product_lib.HostScene(20)
     with pytest.raises(ValueError):
         product_lib.HostScene(-1)
+
+
+def test_image_texture_from_pixels_layout_and_fetch(product_lib, oracle):
+    """rt_mat_lambert_image_pixels: the record is the reference's ImageTexture with the payload in the arena, padded by
+    the row and texel its inclusive clamp can address (rt.cu:349-352); the oracle's fetch follows that rule exactly."""
+    import ctypes as C
+    rng = np.random.default_rng(5)
+    tex = rng.random((4, 6, 3), dtype=np.float32)
+    hs = product_lib.HostScene(None)
+    mat = hs.mat_lambert_image_pixels(tex)
+    hs.add_sphere((0, 0, -1), 0.5, mat)
+    hs.add_sphere((0, -100.5, -1), 100.0, hs.mat_lambert_solid((0.5, 0.5, 0.5)))
+    hs.build_bvh()
+    h, r, t = hs.arrays()
+    off = int(h[0, 48:56].copy().view(np.uint64)[0])
+    rec = t[off:off + 32]
+    assert int(rec[0:4].copy().view(np.uint32)[0]) == 2                               # RT_TEX_IMAGE
+    assert int(rec[8:16].copy().view(np.uint64)[0]) != 0                              # "decoded": pixels != NULL
+    px_off = int(rec[16:24].copy().view(np.uint64)[0])
+    assert px_off == off + 32
+    assert tuple(rec[24:32].copy().view(np.int32)) == (6, 4)
+    payload = t[px_off:px_off + ((4 + 1) * 6 + 1) * 12].copy().view(np.float32).reshape(-1, 3)
+    assert np.array_equal(payload[:24], tex.reshape(-1, 3)) and not payload[24:].any()
+    sc = common.oracle_scene(oracle, hs)
+    L = oracle.lib()
+    for (u, v) in [(0.0, 1.0), (0.999, 0.001), (1.0, 0.0), (0.5, 0.5), (-3.0, 7.0), (1.0, 1.0), (0.17, 0.83)]:
+        got = np.zeros(3, dtype=np.float32)
+        L.orc_texture_color(C.byref(sc.c), off, u, v, oracle.fptr(np.zeros(3, dtype=np.float32)), oracle.fptr(got))
+        uc, vc = min(max(u, 0.0), 1.0), 1.0 - min(max(v, 0.0), 1.0)
+        x, y = min(max(int(np.float32(uc) * np.float32(6)), 0), 6), min(max(int(np.float32(vc) * np.float32(4)), 0), 4)
+        assert np.array_equal(got, payload[y * 6 + x]), (u, v)
+    # no pixels / empty image: the missing-file record (magenta), like rt_mat_lambert_image
+    hs2 = product_lib.HostScene(None)
+    m2 = hs2.mat_lambert_image_pixels(np.zeros((0, 0, 3), dtype=np.float32))
+    hs2.add_sphere((0, 0, -1), 0.5, m2)
+    hs2.build_bvh()
+    h2, _, t2 = hs2.arrays()
+    off2 = int(h2[0, 48:56].copy().view(np.uint64)[0])
+    assert int(t2[off2 + 8:off2 + 16].copy().view(np.uint64)[0]) == 0
+    hs.close(); hs2.close()
