@@ -99,11 +99,12 @@ __device__ __forceinline__ bool hit_sphere(const Scene &sc, uint32_t idx, const 
 }
 
 // ---- quad / triangle (rt.cu:1131-1175 with geom_calc_hit 1060-1077) ----
-__device__ __forceinline__ bool planar_inside(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float t, V3 &p,
-                                              float &alpha, float &beta) {
-  const float4 p1 = ldg4(sc.planars + 4 * idx + 1);        // q, w.x
-  const float4 p2 = ldg4(sc.planars + 4 * idx + 2);        // v, w.y
-  const float4 p3 = ldg4(sc.planars + 4 * idx + 3);        // u, w.z
+// EAGER requests the four 16-byte words of the record together, before the plane test decides whether the last three
+// are needed: one exposed load latency per test instead of two, at the price of three loads that most tests do not
+// use.  Measured: pays in the walk with treelets / fused instances (scene 3 +3 %), costs in the plain reference-order
+// walk (Cornell box -5 %), so only the former asks for it.
+__device__ __forceinline__ bool planar_inside_rec(const float4 p1, const float4 p2, const float4 p3, bool triangle, const Ray &r,
+                                                  float t, V3 &p, float &alpha, float &beta) {
   p = along(r.o, t, r.d);
   const V3 pl = vsub(p, v3(p1.x, p1.y, p1.z));
   const V3 w = v3(p1.w, p2.w, p3.w);
@@ -113,9 +114,19 @@ __device__ __forceinline__ bool planar_inside(const Scene &sc, uint32_t idx, boo
   if (triangle) inside = inside && (fadd(alpha, beta) <= 1.0f);
   return inside;
 }
+__device__ __forceinline__ bool planar_inside(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float t, V3 &p,
+                                              float &alpha, float &beta) {
+  const float4 p1 = ldg4(sc.planars + 4 * idx + 1);        // q, w.x
+  const float4 p2 = ldg4(sc.planars + 4 * idx + 2);        // v, w.y
+  const float4 p3 = ldg4(sc.planars + 4 * idx + 3);        // u, w.z
+  return planar_inside_rec(p1, p2, p3, triangle, r, t, p, alpha, beta);
+}
+template <bool EAGER = false>
 __device__ __forceinline__ bool planar_t(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float tmin, float tmax,
                                          float &t_out) {
   const float4 p0 = ldg4(sc.planars + 4 * idx);            // normal, d
+  float4 p1 = p0, p2 = p0, p3 = p0;
+  if (EAGER) { p1 = ldg4(sc.planars + 4 * idx + 1); p2 = ldg4(sc.planars + 4 * idx + 2); p3 = ldg4(sc.planars + 4 * idx + 3); }
   const V3 n = v3(p0.x, p0.y, p0.z);
   const float denom = dot_yfirst(n, r.d);
   // reference: fabsf(denom) >= 1e-8 evaluated in double; (float)1e-8 < 1e-8, so in f32 this is a strict '>'
@@ -123,7 +134,7 @@ __device__ __forceinline__ bool planar_t(const Scene &sc, uint32_t idx, bool tri
   const float t = fdiv(fsub(p0.w, dot_yfirst(n, r.o)), denom);
   if (!(tmin <= t && t <= tmax)) return false;
   V3 p; float alpha, beta;
-  if (!planar_inside(sc, idx, triangle, r, t, p, alpha, beta)) return false;
+  if (EAGER ? !planar_inside_rec(p1, p2, p3, triangle, r, t, p, alpha, beta) : !planar_inside(sc, idx, triangle, r, t, p, alpha, beta)) return false;
   t_out = t;
   return true;
 }
@@ -138,10 +149,11 @@ __device__ __forceinline__ void planar_record(const Scene &sc, uint32_t idx, con
   h.n = h.front ? n : vneg(n);
   h.prim = sc.sphere_count + idx;
 }
+template <bool EAGER = false>
 __device__ __forceinline__ bool hit_planar(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float tmin, float &tmax,
                                            Hit &h) {
   float t;
-  if (!planar_t(sc, idx, triangle, r, tmin, tmax, t)) return false;
+  if (!planar_t<EAGER>(sc, idx, triangle, r, tmin, tmax, t)) return false;
   planar_record(sc, idx, r, t, h);
   tmax = t;
   return true;
@@ -218,7 +230,7 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
       case rtd::K_TRIANGLE:
       case rtd::K_QUAD:
         cnt.planar();
-        if (hit_planar(sc, idx, rtd::ref_kind(cur) == rtd::K_TRIANGLE, r, tmin, tmax, h)) {
+        if (hit_planar<TREELETS>(sc, idx, rtd::ref_kind(cur) == rtd::K_TRIANGLE, r, tmin, tmax, h)) {
           result = true; if (in_translation || in_rotation) was_last_hit = true;
         }
         break;
@@ -227,8 +239,12 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
         const float4 n1 = ldg4(sc.ref_nodes + 2 * idx + 1);
         float t0 = tmin, t1 = tmax;
         cnt.box(1);
-        if (aabb_axis(n0.x, n0.y, r.o.x, inv.x, t0, t1) && aabb_axis(n0.z, n0.w, r.o.y, inv.y, t0, t1) &&
-            aabb_axis(n1.x, n1.y, r.o.z, inv.z, t0, t1)) {
+        // all three axes, then one branch (the reference leaves after the first axis that fails; evaluating the others
+        // cannot change the verdict, and both node words are needed at once, so their loads go out together)
+        const bool ax = aabb_axis(n0.x, n0.y, r.o.x, inv.x, t0, t1);
+        const bool ay = aabb_axis(n0.z, n0.w, r.o.y, inv.y, t0, t1);
+        const bool az = aabb_axis(n1.x, n1.y, r.o.z, inv.z, t0, t1);
+        if (ax & ay & az) {
           RT_PUSH(__float_as_uint(n1.w));    // right first => left is visited first (Q11)
           RT_PUSH(__float_as_uint(n1.z));
         }
@@ -327,7 +343,7 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
               break;
             }
             if (ck == rtd::K_SPHERE) { cnt.sphere(); hit_in = hit_sphere(sc, ci, r, a, tmin, tmax, h); }
-            else { cnt.planar(); hit_in = hit_planar(sc, ci, ck == rtd::K_TRIANGLE, r, tmin, tmax, h); }
+            else { cnt.planar(); hit_in = hit_planar<true>(sc, ci, ck == rtd::K_TRIANGLE, r, tmin, tmax, h); }
             if (hit_in) result = true;
           } else {                                          // the way out of a structure instance
             hit_in = was_last_hit;
