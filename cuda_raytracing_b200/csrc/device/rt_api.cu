@@ -66,6 +66,7 @@ struct rt_context {
   uint32_t fuse_min = 8;                                   // env RT_FUSE_MIN: wrapper chains around one object become one item when there are this many (0 = never)
   uint32_t treelet_min = 8;                                // env RT_TREELET_MIN: smallest wrapper-free subtree given an own BVH (0 = none)
   int tile_w = 8;                                          // work items walk 8x4-pixel tiles; env RT_TILE_W (1..32, power of 2)
+  int scatter = -1;                                        // item order: -1 automatic, 0 tile order, 1 scattered; env RT_SCATTER
   uint64_t rng_seed = 0, rng_first = 0, rng_count = 0, rng_bands = 0; bool rng_valid = false;   // what b_rng_init holds
   uint64_t live_seed = 0, live_first = 0, live_count = 0, live_bands = 0; bool live_valid = false;  // what b_rng_states carries on from
   // scratch for rt_render (host-buffer path)
@@ -110,6 +111,7 @@ int rt_context_create(int device_id, rt_context **out) {
   if (const char *v = getenv("RT_TILE_W")) { const long x = strtol(v, nullptr, 10); if (x >= 1 && x <= 32 && (x & (x - 1)) == 0) ctx->tile_w = (int)x; }
   if (const char *v = getenv("RT_FUSE_MIN")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 30)) ctx->fuse_min = (uint32_t)x; }
   if (const char *v = getenv("RT_TREELET_MIN")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 30)) ctx->treelet_min = (uint32_t)x; }
+  if (const char *v = getenv("RT_SCATTER")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->scatter = (int)x; }
   if (const char *v = getenv("RT_CLAIM_GROUP")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= 32) ctx->claim_group = (int)x; }
   std::vector<uint32_t> mats;
   rtp::xorwow_sequence_matrices(mats);
@@ -201,6 +203,16 @@ static int check_params(rt_context *ctx, const rt_render_params *p, int *row0, i
   if (r0 < 0 || r1 > p->img_height || r0 >= r1) return fail(ctx, RT_ERR_INVALID, "rt_render: bad row range");
   *row0 = r0; *row1 = r1;
   return RT_OK;
+}
+
+// golden-ratio stride coprime to n (n >= 64): i -> i * mul mod n is a permutation with well-spread neighbours
+static uint32_t scatter_multiplier(uint32_t n) {
+  uint32_t m = (uint32_t)((double)n * 0.6180339887498949) | 1u;
+  for (;; m += 2) {
+    uint32_t x = m, y = n;
+    while (y) { const uint32_t t = x % y; x = y; y = t; }
+    if (x == 1) return m % n;
+  }
 }
 
 // the rendered set of a call: a run of rows, or interleaved bands of rows (tile sharding in one launch)
@@ -312,6 +324,12 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
     // pixels at once (coherent node visits), small scenes and the reference-order walk from claiming at once
     const bool big_fast = ctx->packed.traversal_used == RT_TRAVERSAL_FAST && ctx->packed.sphere_count + ctx->packed.planar_count >= 64;
     a.claim_group = ctx->claim_group > 0 ? ctx->claim_group : (big_fast ? 32 : 1);
+    // Scenes with Perlin textures are bound by their slowest pixels (profiles/r1_small_images_are_latency_bound.md):
+    // in tile order those pixels fill whole warps, whose every bounce then carries 32 turbulence evaluations while
+    // other SMs idle.  Scattered order spreads them over all warps.  Multiplier: golden-ratio stride, coprime to the
+    // slot count, so slot -> slot * mul mod n is a permutation and neighbours in the queue are far apart in the image.
+    const bool want_scatter = ctx->scatter >= 0 ? ctx->scatter == 1 : (ctx->scene.perlin_tables > 0 && a.claim_group == 1);
+    if (want_scatter && a.slots_per_chunk >= 64) a.scatter_mul = scatter_multiplier(a.slots_per_chunk);
   }
   a.counters = (unsigned long long *)ctx->b_counters.ptr;
   a.stack_entries = (int32_t)ctx->scene.stack_entries;

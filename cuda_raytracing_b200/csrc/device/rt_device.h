@@ -95,6 +95,8 @@ struct RenderArgs {
   unsigned long long item_count;// slots_per_chunk * chunk_count work items; item = chunk * slots_per_chunk + slot
   uint32_t slots_per_chunk;     // 32 * number of 32-pixel tiles covering the rendered rows (>= pixel_count)
   uint32_t tiles_x, tile_shift; // tiles per row of tiles; log2 of the tile width (tile = 2^s x 2^(5-s) pixels)
+  uint32_t scatter_mul;         // 0: slots in tile order; else slot -> slot * scatter_mul mod slots_per_chunk (coprime: a
+                                // permutation), so items claimed together are pixels far apart (scenes bound by slow pixels)
   int32_t first_row;            // first_pixel / img_width
   int32_t band_rows, band_period, band_phase;   // band_rows > 0: row y of the rendered set is image row
                                 // ((y / band_rows) * band_period + band_phase) * band_rows + y % band_rows (interleaved bands)

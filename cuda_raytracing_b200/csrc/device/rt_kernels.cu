@@ -140,6 +140,9 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
             chunk = (int)(item / (unsigned long long)a.slots_per_chunk);
             slot = (uint32_t)(item - (unsigned long long)chunk * (unsigned long long)a.slots_per_chunk);
           }
+          // scattered order: a warp's pixels come from all over the image, so the pixels with the long paths (which
+          // bound a small image: their samples are produced in sequence) do not sit in the same warps
+          if (a.scatter_mul) slot = (uint32_t)(((unsigned long long)slot * a.scatter_mul) % a.slots_per_chunk);
           const uint32_t tile = slot >> 5, l = slot & 31u;
           const uint32_t ty = tile / a.tiles_x, tx = tile - ty * a.tiles_x;
           const uint32_t x = (tx << a.tile_shift) + (l & ((1u << a.tile_shift) - 1u)), y = (ty << (5u - a.tile_shift)) + (l >> a.tile_shift);
