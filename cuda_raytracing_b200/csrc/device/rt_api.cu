@@ -58,7 +58,7 @@ struct rt_context {
   rtd::Scene scene{};
   rtp::PackedScene packed;
   DeviceBuffer b_ref_nodes, b_xforms, b_instances, b_structs, b_struct_children, b_fast_nodes, b_spheres, b_planars, b_materials,
-      b_checkers, b_perlin_vec, b_perlin_perm, b_arena;
+      b_checkers, b_perlin_vec, b_perlin_perm, b_arena, b_program;
   // rng
   DeviceBuffer b_rng_mats, b_rng_init, b_rng_states, b_progress, b_counters;   // b_rng_init: pristine states (cache)
   int chunk_samples = 0;                                   // 0 = automatic; env RT_CHUNK overrides (tuning knob)
@@ -66,7 +66,8 @@ struct rt_context {
   uint32_t fuse_min = 8;                                   // env RT_FUSE_MIN: wrapper chains around one object become one item when there are this many (0 = never)
   uint32_t treelet_min = 8;                                // env RT_TREELET_MIN: smallest wrapper-free subtree given an own BVH (0 = none)
   int tile_w = 8;                                          // work items walk 8x4-pixel tiles; env RT_TILE_W (1..32, power of 2)
-  int scatter = -1;                                        // item order: -1 automatic, 0 tile order, 1 scattered; env RT_SCATTER
+  int linear = -1;                                         // scenes that have a linear program walk it (kernel mode 3): -1 automatic (yes), 0 never, 1 same as -1; env RT_LINEAR
+  int scatter = -1;                                        // item order: -1 automatic, 0 tile order, 1 scattered pixels, 2 scattered tiles; env RT_SCATTER
   uint64_t rng_seed = 0, rng_first = 0, rng_count = 0, rng_bands = 0; bool rng_valid = false;   // what b_rng_init holds
   uint64_t live_seed = 0, live_first = 0, live_count = 0, live_bands = 0; bool live_valid = false;  // what b_rng_states carries on from
   // scratch for rt_render (host-buffer path)
@@ -111,7 +112,8 @@ int rt_context_create(int device_id, rt_context **out) {
   if (const char *v = getenv("RT_TILE_W")) { const long x = strtol(v, nullptr, 10); if (x >= 1 && x <= 32 && (x & (x - 1)) == 0) ctx->tile_w = (int)x; }
   if (const char *v = getenv("RT_FUSE_MIN")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 30)) ctx->fuse_min = (uint32_t)x; }
   if (const char *v = getenv("RT_TREELET_MIN")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 30)) ctx->treelet_min = (uint32_t)x; }
-  if (const char *v = getenv("RT_SCATTER")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->scatter = (int)x; }
+  if (const char *v = getenv("RT_LINEAR")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->linear = (int)x; }
+  if (const char *v = getenv("RT_SCATTER")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 2) ctx->scatter = (int)x; }
   if (const char *v = getenv("RT_CLAIM_GROUP")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= 32) ctx->claim_group = (int)x; }
   std::vector<uint32_t> mats;
   rtp::xorwow_sequence_matrices(mats);
@@ -129,7 +131,7 @@ void rt_context_destroy(rt_context *ctx) {
   cudaStreamSynchronize(ctx->stream);
   DeviceBuffer *all[] = {&ctx->b_ref_nodes, &ctx->b_xforms, &ctx->b_instances, &ctx->b_structs, &ctx->b_struct_children, &ctx->b_fast_nodes,
                          &ctx->b_spheres, &ctx->b_planars, &ctx->b_materials, &ctx->b_checkers, &ctx->b_perlin_vec,
-                         &ctx->b_perlin_perm, &ctx->b_arena, &ctx->b_rng_mats, &ctx->b_rng_init, &ctx->b_rng_states,
+                         &ctx->b_perlin_perm, &ctx->b_arena, &ctx->b_program, &ctx->b_rng_mats, &ctx->b_rng_init, &ctx->b_rng_states,
                          &ctx->b_progress, &ctx->b_counters,
                          &ctx->b_pixels, &ctx->b_rgb8};
   for (DeviceBuffer *b : all) b->release();
@@ -163,19 +165,21 @@ int rt_scene_upload(rt_context *ctx, const rt_scene_desc *desc, uint32_t travers
   ctx->has_scene = false;
   ctx->packed = rtp::PackedScene();
   rtp::PackedScene &p = ctx->packed;
-  int rc = rtp::pack_scene(*desc, traversal, p, ctx->treelet_min, ctx->fuse_min);
+  int rc = rtp::pack_scene(*desc, traversal, p, ctx->treelet_min, ctx->fuse_min, ctx->linear == 0 ? 0u : rtp::PROGRAM_MAX_DEFAULT);
   if (rc != RT_OK) return fail(ctx, rc, p.error);
   cudaStream_t s = ctx->stream;
 #define UP(buf, vec) RT_CUDA(ctx, ctx->buf.upload((vec).data(), (vec).size() * sizeof((vec)[0]), s))
   UP(b_ref_nodes, p.ref_nodes); UP(b_xforms, p.xforms); UP(b_instances, p.instances); UP(b_structs, p.structures); UP(b_struct_children, p.struct_children);
   UP(b_fast_nodes, p.fast_nodes); UP(b_spheres, p.spheres); UP(b_planars, p.planars); UP(b_materials, p.materials);
   UP(b_checkers, p.checkers); UP(b_perlin_vec, p.perlin_vectors); UP(b_perlin_perm, p.perlin_perm); UP(b_arena, p.tex_arena);
+  UP(b_program, p.program);
 #undef UP
   RT_CUDA(ctx, cudaStreamSynchronize(s));       // the host vectors may be reused after return
   rtd::Scene &sc = ctx->scene;
   sc.ref_nodes = (const float4 *)ctx->b_ref_nodes.ptr; sc.xforms = (const float4 *)ctx->b_xforms.ptr;
   sc.instances = (const float4 *)ctx->b_instances.ptr;
   sc.structures = (const uint2 *)ctx->b_structs.ptr; sc.struct_children = (const uint32_t *)ctx->b_struct_children.ptr;
+  sc.program = (const float4 *)ctx->b_program.ptr; sc.program_ops = (uint32_t)(p.program.size() / 2);
   sc.ref_root = p.ref_root; sc.fast_nodes = (const float4 *)ctx->b_fast_nodes.ptr; sc.fast_root = p.fast_root;
   sc.spheres = (const float4 *)ctx->b_spheres.ptr; sc.planars = (const float4 *)ctx->b_planars.ptr;
   sc.sphere_count = p.sphere_count; sc.planar_count = p.planar_count;
@@ -189,6 +193,14 @@ int rt_scene_upload(rt_context *ctx, const rt_scene_desc *desc, uint32_t travers
   }
   ctx->has_scene = true;
   return RT_OK;
+}
+
+// kernel variant: 1 = own BVH over the whole scene, 3 = reference order as a linear program (small scenes with wrappers),
+// 2 = reference order with treelets / fused instances, 0 = reference order through the stack
+static int kernel_mode(const rtp::PackedScene &p) {
+  if (p.traversal_used == RT_TRAVERSAL_FAST) return 1;
+  if (p.treelets + p.fused_instances > 0) return 2;
+  return p.program.empty() ? 0 : 3;
 }
 
 static int check_params(rt_context *ctx, const rt_render_params *p, int *row0, int *row1) {
@@ -324,12 +336,30 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
     // pixels at once (coherent node visits), small scenes and the reference-order walk from claiming at once
     const bool big_fast = ctx->packed.traversal_used == RT_TRAVERSAL_FAST && ctx->packed.sphere_count + ctx->packed.planar_count >= 64;
     a.claim_group = ctx->claim_group > 0 ? ctx->claim_group : (big_fast ? 32 : 1);
-    // Scenes with Perlin textures are bound by their slowest pixels (profiles/r1_small_images_are_latency_bound.md):
-    // in tile order those pixels fill whole warps, whose every bounce then carries 32 turbulence evaluations while
-    // other SMs idle.  Scattered order spreads them over all warps.  Multiplier: golden-ratio stride, coprime to the
-    // slot count, so slot -> slot * mul mod n is a permutation and neighbours in the queue are far apart in the image.
-    const bool want_scatter = ctx->scatter >= 0 ? ctx->scatter == 1 : (ctx->scene.perlin_tables > 0 && a.claim_group == 1);
-    if (want_scatter && a.slots_per_chunk >= 64) a.scatter_mul = scatter_multiplier(a.slots_per_chunk);
+    // Item order (measured, profiles/r1_item_order_scatter.jsonl).  Tile order keeps neighbouring pixels in one warp and
+    // neighbouring tiles on one SM (coherent walks, L1 hits): scattering costs C1 +40 %, C2 +70 %, scene 3 at 4K +34 %.
+    // It pays where the render is short and bound by WHERE its slow pixels sit rather than by throughput:
+    //  (a) a tiny image (every pixel resident at once, <= 2 per lane): the slow pixels otherwise fill whole warps whose
+    //      every bounce then carries 32 Perlin evaluations (scene 17 at 400x400: 29.8 -> 27.2 ms with 4 time slices per
+    //      pixel instead of 24 -- spreading the pixels already does what the many slices did);
+    //  (b) the hybrid walk on a short render (scene 3 at 800x800: s16 136 -> 108 ms, s64 412 -> 390 ms): in tile order the
+    //      queue ends with the image's heaviest rows.
+    // Multiplier: golden-ratio stride, coprime to the slot count, so slot -> slot * mul mod n is a permutation and
+    // neighbours in the queue are far apart in the image.
+    const double lanes_resident = (double)ctx->sm_count * (ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? 768.0 : 640.0);
+    const bool tiny_image = a.claim_group == 1 && (double)count <= 2.0 * lanes_resident;
+    const bool short_hybrid = kernel_mode(ctx->packed) == 2 &&
+                              count <= (1u << 20) && (double)spp * (double)count <= 1024.0 * lanes_resident;
+    const bool want_scatter = ctx->scatter >= 0 ? ctx->scatter == 1 : (tiny_image || short_hybrid);
+    if (want_scatter && a.slots_per_chunk >= 64) {
+      a.scatter_mul = scatter_multiplier(a.slots_per_chunk);
+      if (ctx->chunk_samples <= 0 && tiny_image && ctx->scatter < 0 && a.chunk_samples < (spp + 3) / 4) {   // at most 4 slices
+        a.chunk_samples = (spp + 3) / 4;
+        a.chunk_count = (spp + a.chunk_samples - 1) / a.chunk_samples;
+        a.item_count = (unsigned long long)a.slots_per_chunk * (unsigned long long)a.chunk_count;
+      }
+    }
+    if (ctx->scatter == 2 && a.slots_per_chunk >= 64 * 32) a.scatter_tile_mul = scatter_multiplier(a.slots_per_chunk >> 5);
   }
   a.counters = (unsigned long long *)ctx->b_counters.ptr;
   a.stack_entries = (int32_t)ctx->scene.stack_entries;
@@ -344,8 +374,8 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   a.resume = resume ? 1u : 0u;
   a.count_rays = (p->flags & (RT_RENDER_COUNT_RAYS | RT_RENDER_COUNT_OPS)) ? 1u : 0u;
   a.count_ops = (p->flags & RT_RENDER_COUNT_OPS) ? 1u : 0u;
-  // kernel variant: 1 = own BVH over the whole scene, 2 = reference order with treelets, 0 = reference order
-  const int mode = ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? 1 : (ctx->packed.treelets + ctx->packed.fused_instances > 0 ? 2 : 0);
+  const int mode = kernel_mode(ctx->packed);
+  if (mode == 3) a.stack_entries = 0;                      // the linear program needs no traversal stack
   RT_CUDA(ctx, rtk::launch_render(a, mode, ctx->sm_count, s, &ctx->last_launch));
   ++launches;
   if (stats) {
@@ -451,7 +481,7 @@ int rt_probe_trace(rt_context *ctx, uint64_t n, const float *origins, const floa
   RT_CUDA(ctx, to_device(o, origins, 3 * n, s)); RT_CUDA(ctx, to_device(d, directions, 3 * n, s));
   if (times) RT_CUDA(ctx, to_device(t, times, n, s));
   RT_CUDA(ctx, r.reserve(n * sizeof(rt_probe_hit)));
-  const int mode = ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? 1 : 0;
+  const int mode = kernel_mode(ctx->packed) == 2 ? 0 : kernel_mode(ctx->packed);   // the stack walk covers treelets / instances
   cudaError_t e = rtk::launch_probe_trace(ctx->scene, mode, n, (const float *)o.ptr, (const float *)d.ptr,
                                           times ? (const float *)t.ptr : nullptr, tmin, tmax, (rt_probe_hit *)r.ptr, s);
   if (e == cudaSuccess) e = cudaMemcpyAsync(out, r.ptr, n * sizeof(rt_probe_hit), cudaMemcpyDeviceToHost, s);
@@ -522,7 +552,9 @@ int rt_scene_pack_info(const rt_scene_desc *scene, uint32_t traversal, uint32_t 
   if (rc != RT_OK) return fail(nullptr, rc, p.error);
   memset(out, 0, sizeof(*out));
   out->traversal_used = p.traversal_used;
-  out->kernel_mode = p.traversal_used == RT_TRAVERSAL_FAST ? 1u : (p.treelets + p.fused_instances > 0 ? 2u : 0u);
+  out->kernel_mode = (uint32_t)kernel_mode(p);
+  out->program_ops = (uint32_t)(p.program.size() / 2);
+  out->program_boxes = p.program_boxes; out->program_prims = p.program_prims; out->program_wrappers = p.program_wrappers;
   out->spheres = p.sphere_count; out->planars = p.planar_count;
   out->own_nodes = (uint32_t)(p.fast_nodes.size() / 4);
   out->treelets = p.treelets; out->treelet_prims = p.treelet_prims; out->fused_instances = p.fused_instances;

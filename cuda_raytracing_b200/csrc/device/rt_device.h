@@ -65,6 +65,13 @@ struct Scene {
   const uint32_t *struct_children;
   const float4 *instances;      // 2 per fused instance: {offset.xyz, child ref} {sin, cos, INST_* flags, 0}
   uint32_t ref_root;            // tagged ref of the reference's root BVH node
+  // the same walk as a linear program (small scenes; trace_linear): 2 x float4 per op, op i is followed by op i + 1
+  //   box          {x0,x1,y0,y1} {z0,z1, skip op (a missed box continues there), K_BVH}
+  //   primitive    {0,0,0,0}     {0,0, sphere / planar index, K_SPHERE|K_TRIANGLE|K_QUAD (| OP_IN_WRAPPER)}
+  //   translation  {offset,0}    {0,0,0, K_TRANSLATION (way in) | OP_T_EXIT (way out)}
+  //   y-rotation   {sin,cos,0,0} {0,0,0, K_YROTATION (way in) | OP_R_EXIT (way out)}
+  const float4 *program;
+  uint32_t program_ops;         // 0: the scene has no program (too big, or wrappers nested in a way only the stack walk mirrors)
   uint32_t stack_entries;       // traversal stack entries per thread this scene's walk can need (<= STACK_CAPACITY)
   // own BVH over world-space primitives (RT_TRAVERSAL_FAST): 4 x float4 per node
   //   n0 = {c0.x0, c0.x1, c0.y0, c0.y1}  n1 = {c1.x0, c1.x1, c1.y0, c1.y1}
@@ -97,6 +104,8 @@ struct RenderArgs {
   uint32_t tiles_x, tile_shift; // tiles per row of tiles; log2 of the tile width (tile = 2^s x 2^(5-s) pixels)
   uint32_t scatter_mul;         // 0: slots in tile order; else slot -> slot * scatter_mul mod slots_per_chunk (coprime: a
                                 // permutation), so items claimed together are pixels far apart (scenes bound by slow pixels)
+  uint32_t scatter_tile_mul;    // 0: tiles in row-major order; else tile -> tile * mul mod tile count: the 32 pixels of a tile
+                                // stay together (coherent warps), consecutive tiles are far apart (no heavy region left for the end)
   int32_t first_row;            // first_pixel / img_width
   int32_t band_rows, band_period, band_phase;   // band_rows > 0: row y of the rendered set is image row
                                 // ((y / band_rows) * band_period + band_phase) * band_rows + y % band_rows (interleaved bands)

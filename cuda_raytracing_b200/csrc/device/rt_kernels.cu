@@ -41,6 +41,10 @@ constexpr int RT_MIN_BLOCKS_FAST = RT_MIN_BLOCKS_PER_SM, RT_MIN_BLOCKS_REF = RT_
 #else
 constexpr int RT_MIN_BLOCKS_FAST = 6, RT_MIN_BLOCKS_REF = 5;
 #endif
+#ifndef RT_MIN_BLOCKS_LINEAR
+#define RT_MIN_BLOCKS_LINEAR 5
+#endif
+constexpr int min_blocks(int mode) { return mode == 1 ? RT_MIN_BLOCKS_FAST : (mode == 3 ? RT_MIN_BLOCKS_LINEAR : RT_MIN_BLOCKS_REF); }
 
 __device__ __forceinline__ void stage_perlin(const Scene &sc, PerlinSmem *dst) {
   for (int i = threadIdx.x; i < 256; i += blockDim.x) {
@@ -79,7 +83,7 @@ __device__ __forceinline__ size_t image_pixel(const RenderArgs &a, int pix) {
 }
 
 template <int MODE, int MAXB, bool COUNT>
-__global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_MIN_BLOCKS_REF) render_kernel(const RenderArgs a) {
+__global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(const RenderArgs a) {
   extern __shared__ __align__(16) uint32_t smem[];
   const Scene &sc = a.scene;
   uint32_t *stk = smem + threadIdx.x;
@@ -143,7 +147,9 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
           // scattered order: a warp's pixels come from all over the image, so the pixels with the long paths (which
           // bound a small image: their samples are produced in sequence) do not sit in the same warps
           if (a.scatter_mul) slot = (uint32_t)(((unsigned long long)slot * a.scatter_mul) % a.slots_per_chunk);
-          const uint32_t tile = slot >> 5, l = slot & 31u;
+          uint32_t tile = slot >> 5;
+          const uint32_t l = slot & 31u;
+          if (a.scatter_tile_mul) tile = (uint32_t)(((unsigned long long)tile * a.scatter_tile_mul) % (a.slots_per_chunk >> 5));
           const uint32_t ty = tile / a.tiles_x, tx = tile - ty * a.tiles_x;
           const uint32_t x = (tx << a.tile_shift) + (l & ((1u << a.tile_shift) - 1u)), y = (ty << (5u - a.tile_shift)) + (l >> a.tile_shift);
           if (x < (uint32_t)a.img_width && y * (uint32_t)a.img_width + x < (uint32_t)a.pixel_count) {
@@ -201,10 +207,18 @@ __global__ void __launch_bounds__(RT_BLOCK, MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_
     bool done = live && (budget <= 0);
     bool noise_pending = false;                           // this bounce's attenuation is a Perlin texture, evaluated below
     V3 noise_p = cam; float noise_scale = 0.0f;
+    Hit hl; bool hit_l = false;                           // MODE 3: the whole warp walks the scene's program together
+    if (MODE == 3) {
+      hl.u = 0.0f; hl.v = 0.0f; hl.t = 0.0f; hl.prim = 0; hl.front = 0; hl.p = cam; hl.n = cam;
+      hit_l = rtt::trace_linear(sc, ray, 0.001f, __uint_as_float(0x7f800000u), hl, live && !done, cnt);
+    }
     if (live && !done) {
       ++rays;
       Hit h; h.u = 0.0f; h.v = 0.0f; h.t = 0.0f; h.prim = 0; h.front = 0; h.p = cam; h.n = cam;
-      if (trace<MODE>(sc, ray, h, stk, stride, cnt)) {
+      bool hit_any;
+      if (MODE == 3) { h = hl; hit_any = hit_l; }
+      else hit_any = trace<MODE>(sc, ray, h, stk, stride, cnt);
+      if (hit_any) {
         const uint4 m0 = __ldg(sc.materials + 2 * h.prim);
         if (COUNT) {
           const uint32_t ty = m0.x & 0xffu, tk = (m0.x >> 8) & 0xffu;
@@ -394,15 +408,17 @@ __global__ void __launch_bounds__(PROBE_BLOCK) probe_trace_kernel(const Scene sc
                                                                   float tmin, float tmax, rt_probe_hit *__restrict__ out) {
   extern __shared__ __align__(16) uint32_t smem[];
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+  if (MODE != 3 && i >= n) return;                        // the linear walk is a whole-warp job: idle lanes stay for the votes
+  const uint64_t j = i < n ? i : n - 1;
   Ray r;
-  r.o = v3(org[3 * i], org[3 * i + 1], org[3 * i + 2]);
-  r.d = v3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
-  r.time = times ? times[i] : 0.0f;
+  r.o = v3(org[3 * j], org[3 * j + 1], org[3 * j + 2]);
+  r.d = v3(dir[3 * j], dir[3 * j + 1], dir[3 * j + 2]);
+  r.time = times ? times[j] : 0.0f;
   Hit h; h.u = 0.0f; h.v = 0.0f; h.t = 0.0f; h.prim = 0; h.front = 0; h.p = v3(0, 0, 0); h.n = v3(0, 0, 0);
   bool hit;
   rtt::NoCount cnt;
   if (MODE == 0) hit = rtt::trace_reference<true>(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
+  else if (MODE == 3) { hit = rtt::trace_linear(sc, r, tmin, tmax, h, i < n, cnt); if (i >= n) return; }
   else hit = rtt::trace_fast(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
   rt_probe_hit o;
   o.origin[0] = r.o.x; o.origin[1] = r.o.y; o.origin[2] = r.o.z;
@@ -452,6 +468,7 @@ cudaError_t launch_probe_trace(const rtd::Scene &scene, int mode, uint64_t n, co
   if (n == 0) return cudaSuccess;
   const size_t smem = sizeof(uint32_t) * rtd::STACK_CAPACITY * PROBE_BLOCK;
   if (mode == 0) probe_trace_kernel<0><<<probe_grid(n), PROBE_BLOCK, smem, stream>>>(scene, n, origins, directions, times, tmin, tmax, out);
+  else if (mode == 3) probe_trace_kernel<3><<<probe_grid(n), PROBE_BLOCK, 0, stream>>>(scene, n, origins, directions, times, tmin, tmax, out);
   else probe_trace_kernel<1><<<probe_grid(n), PROBE_BLOCK, smem, stream>>>(scene, n, origins, directions, times, tmin, tmax, out);
   return cudaGetLastError();
 }
@@ -485,7 +502,7 @@ static cudaError_t launch_render_t(const RenderArgs &args, int sm_count, cudaStr
   // everything else stays cache); env RT_CARVEOUT = percent overrides (tuning knob)
   int carve = 50;
   {
-    constexpr int want_blocks = MODE == 1 ? RT_MIN_BLOCKS_FAST : RT_MIN_BLOCKS_REF;
+    constexpr int want_blocks = min_blocks(MODE);
     const size_t need = (size_t)want_blocks * (smem + 1024 + 1024);     // + static + the per-block reservation
     carve = (int)((need * 100 + 228 * 1024 - 1) / (228 * 1024)) + 3;
     if (carve > 100) carve = 100;
@@ -516,10 +533,12 @@ cudaError_t launch_render(const rtd::RenderArgs &args, int mode, int sm_count, c
   if (args.count_ops) {                                  // instrumented build of the same kernel (not the timed one)
     if (mode == 0) return launch_render_t<0, 256, true>(args, sm_count, stream, info);
     if (mode == 2) return launch_render_t<2, 256, true>(args, sm_count, stream, info);
+    if (mode == 3) return launch_render_t<3, 256, true>(args, sm_count, stream, info);
     return launch_render_t<1, 256, true>(args, sm_count, stream, info);
   }
   if (mode == 0) return small ? launch_render_t<0, 64, false>(args, sm_count, stream, info) : launch_render_t<0, 256, false>(args, sm_count, stream, info);
   if (mode == 2) return small ? launch_render_t<2, 64, false>(args, sm_count, stream, info) : launch_render_t<2, 256, false>(args, sm_count, stream, info);
+  if (mode == 3) return small ? launch_render_t<3, 64, false>(args, sm_count, stream, info) : launch_render_t<3, 256, false>(args, sm_count, stream, info);
   return small ? launch_render_t<1, 64, false>(args, sm_count, stream, info) : launch_render_t<1, 256, false>(args, sm_count, stream, info);
 }
 

@@ -169,7 +169,9 @@ struct Packer {
   uint32_t treelet_min;                         // smallest wrapper-free subtree (primitives) worth an own BVH; 0 = never
   bool fuse_instances;
   uint32_t fuse_min;                            // fewer qualifying chains than this (and no treelet): keep the plain walk
-  Packer(const rt_scene_desc &desc, PackedScene &o, uint32_t tmin, uint32_t fmin) : d(desc), out(o), treelet_min(tmin), fuse_instances(fmin > 0), fuse_min(fmin) {}
+  uint32_t program_max;                         // longest reference-order walk (ops) laid out as a linear program; 0 = never
+  Packer(const rt_scene_desc &desc, PackedScene &o, uint32_t tmin, uint32_t fmin, uint32_t pmax)
+      : d(desc), out(o), treelet_min(tmin), fuse_instances(fmin > 0), fuse_min(fmin), program_max(pmax) {}
 
   const rt_hittable &H(uint32_t i) const { return d.hittables[i]; }
 
@@ -341,6 +343,61 @@ struct Packer {
     }
     return found;
   }
+  // ---- the reference-order walk as a linear program (trace_linear in rt_trace.cuh) ----
+  // Static replay of the stack machine of trace_reference with every box entered: a BVH node pushes right then left (left
+  // is walked first; a leaf node with left == right tests its object twice, as the reference does), a structure pushes
+  // its children in order (the last is walked first), a wrapper is walked as way in / child / way out.  Returns false
+  // when the walk does not fit `program_max` ops or a wrapper sits inside a wrapper of its own kind (the reference's
+  // in_translation / in_rotation flags then mean something only the stack walk mirrors).
+  void program_op(float4 a, float z0, float z1, uint32_t arg, uint32_t code) {
+    out.program.push_back(a);
+    out.program.push_back(f4(z0, z1, as_float(arg), as_float(code)));
+  }
+  bool emit_program(uint32_t href, bool in_t, bool in_r, int guard) {
+    if (guard > 64 || href >= d.hittable_count || out.program.size() / 2 >= program_max) return false;
+    const rt_hittable &h = H(href);
+    const uint32_t inside = (in_t || in_r) ? 0x100u : 0u;
+    switch (h.type) {
+      case RT_OBJ_SPHERE: case RT_OBJ_TRIANGLE: case RT_OBJ_QUAD:
+        program_op(f4(0, 0, 0, 0), 0, 0, ref_index(tag[href]), ref_kind(tag[href]) | inside);
+        ++out.program_prims;
+        return true;
+      case RT_OBJ_BVH_NODE: {
+        if (h.u.bvh.left >= d.world_count || h.u.bvh.right >= d.world_count) return false;
+        const size_t me = out.program.size() / 2;
+        const rt_aabb &b = h.u.bvh.bbox;
+        program_op(f4(b.x0, b.x1, b.y0, b.y1), b.z0, b.z1, 0, K_BVH);
+        ++out.program_boxes;
+        if (!emit_program(d.world_refs[h.u.bvh.left], in_t, in_r, guard + 1)) return false;
+        if (!emit_program(d.world_refs[h.u.bvh.right], in_t, in_r, guard + 1)) return false;
+        out.program[2 * me + 1].z = as_float((uint32_t)(out.program.size() / 2));
+        return true;
+      }
+      case RT_OBJ_TRANSLATION: {
+        if (in_t) return false;
+        const rt_vec3 &o = h.u.translation.offset;
+        program_op(f4(o.x, o.y, o.z, 0), 0, 0, 0, K_TRANSLATION);
+        ++out.program_wrappers;
+        if (!emit_program(h.u.translation.child, true, in_r, guard + 1)) return false;
+        program_op(f4(o.x, o.y, o.z, 0), 0, 0, 0, 6u);
+        return out.program.size() / 2 <= program_max;
+      }
+      case RT_OBJ_Y_ROTATION: {
+        if (in_r) return false;
+        program_op(f4(h.u.y_rotation.sin_theta, h.u.y_rotation.cos_theta, 0, 0), 0, 0, 0, K_YROTATION);
+        ++out.program_wrappers;
+        if (!emit_program(h.u.y_rotation.child, in_t, true, guard + 1)) return false;
+        program_op(f4(h.u.y_rotation.sin_theta, h.u.y_rotation.cos_theta, 0, 0), 0, 0, 0, 7u);
+        return out.program.size() / 2 <= program_max;
+      }
+      case RT_OBJ_STRUCTURE:
+        if ((uint64_t)h.u.structure.first + h.u.structure.count > d.hittable_count) return false;
+        for (uint32_t k = h.u.structure.count; k-- > 0;)
+          if (!emit_program(h.u.structure.first + k, in_t, in_r, guard + 1)) return false;
+        return true;
+      default: return false;
+    }
+  }
   static void center_leaf(Leaf &lf) { for (int a = 0; a < 3; ++a) lf.centroid[a] = 0.5f * (lf.box.lo[a] + lf.box.hi[a]); }
 
   // world-space copy of everything below `href` (FAST traversal)
@@ -478,6 +535,12 @@ struct Packer {
     const uint32_t root_href = d.world_refs[d.root_wref];
     out.ref_root = tag[root_href];
     out.ref_stack_need = stack_need(root_href, 0, 0) + 1;
+    // small scenes with wrappers (where neither treelets nor fused instances were worth planting): the same walk as a
+    // linear program.  RT_TRAVERSAL_REFERENCE stays the literal stack walk (the mode to bisect against).
+    if (traversal == RT_TRAVERSAL_AUTO && !want_fast && program_max > 0 && out.treelets + out.fused_instances == 0 &&
+        !emit_program(root_href, false, false, 0)) {
+      out.program.clear(); out.program_boxes = out.program_prims = out.program_wrappers = 0;
+    }
 
     // own BVH over the whole scene
     if (want_fast) {
@@ -523,9 +586,10 @@ struct Packer {
 
 }  // namespace
 
-int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out, uint32_t treelet_min, uint32_t fuse_min) {
+int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out, uint32_t treelet_min, uint32_t fuse_min,
+               uint32_t program_max) {
   if (traversal > RT_TRAVERSAL_FAST) { out.error = "rt_scene_upload: unknown traversal mode"; return RT_ERR_INVALID; }
-  Packer p(desc, out, treelet_min, fuse_min);
+  Packer p(desc, out, treelet_min, fuse_min, program_max);
   return p.run(traversal);
 }
 

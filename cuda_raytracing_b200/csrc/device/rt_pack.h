@@ -14,6 +14,8 @@ namespace rtp {
 
 struct PackedScene {
   std::vector<float4> ref_nodes, xforms, instances, fast_nodes, spheres, planars, checkers, perlin_vectors;
+  std::vector<float4> program;           // reference-order walk as a linear program (2 per op), empty when not available
+  uint32_t program_boxes = 0, program_prims = 0, program_wrappers = 0;   // op counts by kind (wrappers: ways in)
   std::vector<uint2> structures;
   std::vector<uint32_t> struct_children;
   std::vector<uint4> materials;          // 2 per primitive id
@@ -35,8 +37,11 @@ struct PackedScene {
 // at least this many primitives by an own SAH BVH (0 = never)
 // fuse_min: the same mode does translation / y-rotation chains around one object as one item of the walk when the scene
 // has a treelet or at least this many such chains (0 = never)
+// program_max: a scene with wrappers whose whole reference-order walk fits this many ops also gets the linear program
+// (rt_device.h Scene::program; 0 = never)
+constexpr uint32_t PROGRAM_MAX_DEFAULT = 256;
 int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out, uint32_t treelet_min = 8,
-               uint32_t fuse_min = 8);
+               uint32_t fuse_min = 8, uint32_t program_max = PROGRAM_MAX_DEFAULT);
 
 // one reference Material (24 B) -> the two 16-byte words of a device material record, pre-resolving its
 // texture against `arena`; may append to out.checkers / perlin tables.

@@ -397,6 +397,100 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
   return result;
 }
 
+// ================= reference order as a linear program (small scenes with wrappers) ============================
+// The reference's walk has a FIXED visiting order: a BVH node pushes right then left, a structure its children in order,
+// a wrapper itself (the way out) and its child; nothing depends on the ray except WHETHER a node's box is entered.  The
+// packer therefore lays the whole walk out as a program (rt_device.h, Scene::program): op i is followed by op i + 1,
+// except that a box that is missed continues at its `skip` op (the first op after its subtree).  No stack.
+// All 32 lanes of a warp run the program together: each step executes the LOWEST op any lane still has to do
+// (redux.sync min), for the lanes that are at it.  The op is warp-uniform, so its kind is a uniform branch and its
+// record a broadcast load, and an op is issued at most once per warp and ray -- where the stack walk issues it once
+// per group of lanes that reach it at the same time.  Per lane the operations and their order are those of
+// trace_reference<false> (same helpers, same roundings, same drift of the ray through the wrappers).
+// Must be called by all 32 lanes; lanes with active == false only take part in the votes.
+constexpr uint32_t OP_T_EXIT = 6u, OP_R_EXIT = 7u, OP_IN_WRAPPER = 0x100u;
+template <class C>
+__device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin, float tmax, Hit &h, const bool active, C &cnt) {
+  bool result = false, was_last_hit = false;
+  V3 inv = v3(frcp(r.d.x), frcp(r.d.y), frcp(r.d.z));
+  float a = dot_xfirst(r.d, r.d);
+  const uint32_t n_ops = sc.program_ops;
+  uint32_t pc = active ? 0u : 0xffffffffu;
+  for (;;) {
+    const uint32_t cur = __reduce_min_sync(0xffffffffu, pc);
+    if (cur >= n_ops) break;
+    const float4 w0 = ldg4(sc.program + 2 * cur), w1 = ldg4(sc.program + 2 * cur + 1);
+    const uint32_t code = __float_as_uint(w1.w), arg = __float_as_uint(w1.z);
+    const bool me = pc == cur;
+    if (me) pc = cur + 1u;
+    switch (code & 7u) {
+      case rtd::K_SPHERE:
+        if (me) {
+          cnt.sphere();
+          if (hit_sphere(sc, arg, r, a, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
+        }
+        break;
+      case rtd::K_TRIANGLE:
+      case rtd::K_QUAD:
+        if (me) {
+          cnt.planar();
+          if (hit_planar<true>(sc, arg, (code & 7u) == rtd::K_TRIANGLE, r, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
+        }
+        break;
+      case rtd::K_BVH:
+        if (me) {
+          float t0 = tmin, t1 = tmax;
+          cnt.box(1);
+          const bool ax = aabb_axis(w0.x, w0.y, r.o.x, inv.x, t0, t1);
+          const bool ay = aabb_axis(w0.z, w0.w, r.o.y, inv.y, t0, t1);
+          const bool az = aabb_axis(w1.x, w1.y, r.o.z, inv.z, t0, t1);
+          if (!(ax & ay & az)) pc = arg;
+        }
+        break;
+      case rtd::K_TRANSLATION:
+        if (me) { cnt.translation(); was_last_hit = false; r.o = vsub(r.o, v3(w0.x, w0.y, w0.z)); }
+        break;
+      case OP_T_EXIT:
+        if (me) {
+          const V3 off = v3(w0.x, w0.y, w0.z);
+          cnt.translation();
+          r.o = vadd(r.o, off);
+          if (was_last_hit) h.p = vadd(h.p, off);
+        }
+        break;
+      case rtd::K_YROTATION:
+        if (me) {                                           // rt.cu:1194-1209, roundings from the reference's SASS
+          const float sn = w0.x, cs = w0.y;
+          cnt.rotation();
+          was_last_hit = false;
+          const V3 o = r.o, d = r.d;
+          r.o = v3(ffma(o.x, cs, -fmul(o.z, sn)), o.y, ffma(o.x, sn, fmul(o.z, cs)));
+          r.d = v3(ffma(d.x, cs, -fmul(d.z, sn)), d.y, ffma(d.z, cs, fmul(d.x, sn)));
+          inv.x = frcp(r.d.x); inv.z = frcp(r.d.z);
+          a = dot_xfirst(r.d, r.d);
+        }
+        break;
+      default:                                              // OP_R_EXIT, rt.cu:1210-1236
+        if (me) {
+          const float sn = w0.x, cs = w0.y;
+          cnt.rotation();
+          const V3 o = r.o, d = r.d;
+          r.o = v3(ffma(o.x, cs, fmul(o.z, sn)), o.y, ffma(o.z, cs, -fmul(o.x, sn)));
+          r.d = v3(ffma(d.x, cs, fmul(d.z, sn)), d.y, ffma(d.z, cs, -fmul(d.x, sn)));
+          if (was_last_hit) {
+            const V3 p = h.p, n = h.n;
+            h.p = v3(ffma(p.x, cs, fmul(p.z, sn)), p.y, ffma(p.z, cs, -fmul(p.x, sn)));
+            h.n = v3(ffma(n.x, cs, fmul(n.z, sn)), n.y, ffma(n.z, cs, -fmul(n.x, sn)));
+          }
+          inv.x = frcp(r.d.x); inv.z = frcp(r.d.z);
+          a = dot_xfirst(r.d, r.d);
+        }
+        break;
+    }
+  }
+  return result;
+}
+
 // ================= own BVH (SAH, world-space primitives, near child first) =====================================
 // Closest hit is independent of visiting order and of (conservative) box culling, so for scenes without
 // instance wrappers this returns bit-identical hits to trace_reference at a fraction of the node visits.

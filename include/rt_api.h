@@ -144,12 +144,15 @@ int rt_probe_xorwow(rt_context *ctx, uint64_t seed, uint64_t first_subsequence, 
  * RT_FUSE_MIN knobs (8 / 8 by default). */
 typedef struct rt_pack_info {
   uint32_t traversal_used;                 /* RT_TRAVERSAL_REFERENCE or RT_TRAVERSAL_FAST */
-  uint32_t kernel_mode;                    /* 0 reference order, 1 own BVH, 2 reference order + treelets / fused instances */
+  uint32_t kernel_mode;                    /* 0 reference order, 1 own BVH, 2 reference order + treelets / fused instances,
+                                              3 reference order as a linear program walked by whole warps */
   uint32_t spheres, planars;               /* primitive records (flattened instances included in FAST mode) */
   uint32_t own_nodes;                      /* 64-byte own-BVH nodes (whole scene, or all treelets) */
   uint32_t treelets, treelet_prims, fused_instances;
   uint32_t stack_need, stack_capacity;     /* traversal stack entries per thread */
   uint32_t perlin_tables, has_wrappers;
+  uint32_t program_ops;                    /* ops of the linear program (0: none -- own BVH, too long, or odd wrapper nesting) */
+  uint32_t program_boxes, program_prims, program_wrappers;   /* of which box tests, primitive tests, wrappers (ways in) */
 } rt_pack_info;
 int rt_scene_pack_info(const rt_scene_desc *scene, uint32_t traversal, uint32_t treelet_min, uint32_t fuse_min, rt_pack_info *out);
 

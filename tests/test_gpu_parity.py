@@ -324,17 +324,20 @@ def test_image_does_not_depend_on_scheduling_knobs(product_lib, sid):
 @pytest.mark.parametrize("sid", sorted(WRAPPER_SCENES))
 def test_hybrid_walk_equals_reference_order(product_lib, sid):
     """RT_TRAVERSAL_AUTO on scenes with instance wrappers: treelets (own BVH inside wrapper-free subtrees) and fused
-    instances, forced on even where the packer would not bother, give the image of the literal reference-order walk
-    bit for bit -- and probes return the same hits and the same edited rays."""
+    instances, forced on even where the packer would not bother, and the linear program of the small scenes give the
+    image of the literal reference-order walk bit for bit -- and probes return the same hits and the same edited rays."""
     hs = product_lib.HostScene(sid)
     p = hs.params(96, 6, 12)
     rng = np.random.default_rng(4242 + sid)
     o, d, t = common.scene_rays(hs.settings, rng, 4000)
-    saved = {k: os.environ.get(k) for k in ("RT_FUSE_MIN", "RT_TREELET_MIN")}
+    saved = {k: os.environ.get(k) for k in ("RT_FUSE_MIN", "RT_TREELET_MIN", "RT_LINEAR")}
     results = []
     try:
+        # the literal stack walk; the hybrid walk forced two ways; the automatic choice (small scenes: the linear program
+        # walked by whole warps, kernel mode 3); the automatic choice without the linear program
         for knobs, trav in (({}, product_lib.RT_TRAVERSAL_REFERENCE), ({"RT_FUSE_MIN": "1", "RT_TREELET_MIN": "2"}, product_lib.RT_TRAVERSAL_AUTO),
-                            ({"RT_FUSE_MIN": "0", "RT_TREELET_MIN": "3"}, product_lib.RT_TRAVERSAL_AUTO)):
+                            ({"RT_FUSE_MIN": "0", "RT_TREELET_MIN": "3"}, product_lib.RT_TRAVERSAL_AUTO),
+                            ({}, product_lib.RT_TRAVERSAL_AUTO), ({"RT_LINEAR": "0"}, product_lib.RT_TRAVERSAL_AUTO)):
             for k in saved:
                 os.environ.pop(k, None)
             os.environ.update(knobs)

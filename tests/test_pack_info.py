@@ -15,8 +15,10 @@ def test_every_scene_packs_in_every_mode(product_lib, sid):
         if trav == product_lib.RT_TRAVERSAL_REFERENCE:          # the literal walk: no stand-ins
             assert (i.traversal_used, i.kernel_mode) == (product_lib.RT_TRAVERSAL_REFERENCE, 0)
             assert i.treelets == i.fused_instances == i.own_nodes == 0
+            assert i.program_ops == 0
         if trav == product_lib.RT_TRAVERSAL_AUTO:               # exact results: own BVH only where order cannot matter
             assert i.traversal_used == (product_lib.RT_TRAVERSAL_REFERENCE if i.has_wrappers else product_lib.RT_TRAVERSAL_FAST)
+            assert i.kernel_mode == (1 if not i.has_wrappers else (2 if i.treelets + i.fused_instances else 3))
     hs.close()
 
 
@@ -43,10 +45,24 @@ def test_small_instance_counts_keep_the_plain_walk(product_lib):
     faster); the knobs can force the hybrid walk (the GPU parity test does)."""
     hs = product_lib.HostScene(1)
     i = hs.pack_info()
-    assert (i.kernel_mode, i.treelets, i.fused_instances) == (0, 0, 0)
+    assert (i.kernel_mode, i.treelets, i.fused_instances) == (3, 0, 0)
     forced = hs.pack_info(treelet_min=2, fuse_min=1)
     assert forced.kernel_mode == 2 and forced.fused_instances == 2 and forced.treelets >= 1
     assert forced.stack_need <= forced.stack_capacity
+    hs.close()
+
+
+def test_linear_program_of_the_cornell_box(product_lib):
+    """Scenes with wrappers that are too small for treelets get their reference-order walk laid out as a linear program
+    (kernel mode 3).  Cornell box: 8 top-level objects under the 7 nodes of the reference's BVH; each of the two boxes is
+    translate(rotate(structure of 6 quads)), a structure costs no op (its children are simply walked)."""
+    hs = product_lib.HostScene(1)
+    i = hs.pack_info()
+    assert i.kernel_mode == 3 and i.program_ops == i.program_boxes + i.program_prims + 2 * i.program_wrappers
+    assert i.program_boxes == 7 and i.program_wrappers == 2 * 2 and i.program_prims == 6 + 2 * 6
+    assert i.program_ops == 33                                  # every wrapper is a way in and a way out
+    big = product_lib.HostScene(3).pack_info()                  # 7593 objects: far beyond the program limit, and it has treelets
+    assert big.kernel_mode == 2 and big.program_ops == 0
     hs.close()
 
 
