@@ -66,8 +66,8 @@ struct rt_context {
   uint32_t fuse_min = 8;                                   // env RT_FUSE_MIN: wrapper chains around one object become one item when there are this many (0 = never)
   uint32_t treelet_min = 8;                                // env RT_TREELET_MIN: smallest wrapper-free subtree given an own BVH (0 = none)
   int tile_w = 8;                                          // work items walk 8x4-pixel tiles; env RT_TILE_W (1..32, power of 2)
-  int linear = -1;                                         // scenes that have a linear program walk it (kernel mode 3): -1 automatic (yes), 0 never, 1 same as -1; env RT_LINEAR
-  int scatter = -1;                                        // item order: -1 automatic, 0 tile order, 1 scattered pixels, 2 scattered tiles; env RT_SCATTER
+  int linear = -1;                                         // small scenes with wrappers walk their linear program (kernel mode 3): -1 / 1 yes, 0 never; env RT_LINEAR
+  int scatter = -1;                                        // item order: -1 automatic, 0 tile order, 1 scattered; env RT_SCATTER
   uint64_t rng_seed = 0, rng_first = 0, rng_count = 0, rng_bands = 0; bool rng_valid = false;   // what b_rng_init holds
   uint64_t live_seed = 0, live_first = 0, live_count = 0, live_bands = 0; bool live_valid = false;  // what b_rng_states carries on from
   // scratch for rt_render (host-buffer path)
@@ -113,7 +113,7 @@ int rt_context_create(int device_id, rt_context **out) {
   if (const char *v = getenv("RT_FUSE_MIN")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 30)) ctx->fuse_min = (uint32_t)x; }
   if (const char *v = getenv("RT_TREELET_MIN")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 30)) ctx->treelet_min = (uint32_t)x; }
   if (const char *v = getenv("RT_LINEAR")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->linear = (int)x; }
-  if (const char *v = getenv("RT_SCATTER")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 2) ctx->scatter = (int)x; }
+  if (const char *v = getenv("RT_SCATTER")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->scatter = (int)x; }
   if (const char *v = getenv("RT_CLAIM_GROUP")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= 32) ctx->claim_group = (int)x; }
   std::vector<uint32_t> mats;
   rtp::xorwow_sequence_matrices(mats);
@@ -309,12 +309,13 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   a.pixels = d_pixels;
   a.rng_states = (uint32_t *)ctx->b_rng_states.ptr;
   a.progress = (uint32_t *)ctx->b_progress.ptr;
+  const int mode = kernel_mode(ctx->packed);
+  const double lanes = (double)ctx->sm_count * ((mode == 1 || mode == 3) ? 768.0 : 640.0);   // resident threads: 6 or 5 blocks of 128 per SM
   {   // chunk size: about 1/32 of the samples one resident lane will produce, so that the tail of the render (lanes
       // idle because every remaining pixel is owned) is a few per cent; never below 8 samples per claim
     const int spp = p->samples_per_pixel > 0 ? p->samples_per_pixel : 1;
     int chunk = ctx->chunk_samples;
     if (chunk <= 0) {
-      const double lanes = (double)ctx->sm_count * (ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? 768.0 : 640.0);   // resident threads
       const double per_lane = (double)spp * (double)count / lanes;
       chunk = (int)(per_lane / 32.0);
       if (chunk < 8) chunk = 8;
@@ -346,10 +347,9 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
     //      queue ends with the image's heaviest rows.
     // Multiplier: golden-ratio stride, coprime to the slot count, so slot -> slot * mul mod n is a permutation and
     // neighbours in the queue are far apart in the image.
-    const double lanes_resident = (double)ctx->sm_count * (ctx->packed.traversal_used == RT_TRAVERSAL_FAST ? 768.0 : 640.0);
-    const bool tiny_image = a.claim_group == 1 && (double)count <= 2.0 * lanes_resident;
-    const bool short_hybrid = kernel_mode(ctx->packed) == 2 &&
-                              count <= (1u << 20) && (double)spp * (double)count <= 1024.0 * lanes_resident;
+    const bool tiny_image = a.claim_group == 1 && (double)count <= 2.0 * lanes;
+    const bool short_hybrid = mode == 2 &&
+                              count <= (1u << 20) && (double)spp * (double)count <= 1024.0 * lanes;
     const bool want_scatter = ctx->scatter >= 0 ? ctx->scatter == 1 : (tiny_image || short_hybrid);
     if (want_scatter && a.slots_per_chunk >= 64) {
       a.scatter_mul = scatter_multiplier(a.slots_per_chunk);
@@ -359,7 +359,6 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
         a.item_count = (unsigned long long)a.slots_per_chunk * (unsigned long long)a.chunk_count;
       }
     }
-    if (ctx->scatter == 2 && a.slots_per_chunk >= 64 * 32) a.scatter_tile_mul = scatter_multiplier(a.slots_per_chunk >> 5);
   }
   a.counters = (unsigned long long *)ctx->b_counters.ptr;
   a.stack_entries = (int32_t)ctx->scene.stack_entries;
@@ -374,8 +373,11 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   a.resume = resume ? 1u : 0u;
   a.count_rays = (p->flags & (RT_RENDER_COUNT_RAYS | RT_RENDER_COUNT_OPS)) ? 1u : 0u;
   a.count_ops = (p->flags & RT_RENDER_COUNT_OPS) ? 1u : 0u;
-  const int mode = kernel_mode(ctx->packed);
-  if (mode == 3) a.stack_entries = 0;                      // the linear program needs no traversal stack
+  if (mode == 3) {
+    a.stack_entries = 0;                                   // the linear program needs no traversal stack
+    // short-lived pixels (the regime that gets no time slices either): 5 resident blocks beat 6 (scene 0, s16 b8: 1.13 vs 1.18 ms)
+    if ((long long)a.samples_per_pixel * (long long)(p->max_bounces > 0 ? p->max_bounces : 1) <= 256) a.blocks_per_sm_cap = 5;
+  }
   RT_CUDA(ctx, rtk::launch_render(a, mode, ctx->sm_count, s, &ctx->last_launch));
   ++launches;
   if (stats) {

@@ -67,7 +67,8 @@ struct Scene {
   uint32_t ref_root;            // tagged ref of the reference's root BVH node
   // the same walk as a linear program (small scenes; trace_linear): 2 x float4 per op, op i is followed by op i + 1
   //   box          {x0,x1,y0,y1} {z0,z1, skip op (a missed box continues there), K_BVH}
-  //   primitive    {0,0,0,0}     {0,0, sphere / planar index, K_SPHERE|K_TRIANGLE|K_QUAD (| OP_IN_WRAPPER)}
+  //   primitive    {n.xyz, d} of a quad / triangle (its record's first word), 0 for a sphere
+  //                              {0,0, sphere / planar index, K_SPHERE|K_TRIANGLE|K_QUAD (| OP_IN_WRAPPER)}
   //   translation  {offset,0}    {0,0,0, K_TRANSLATION (way in) | OP_T_EXIT (way out)}
   //   y-rotation   {sin,cos,0,0} {0,0,0, K_YROTATION (way in) | OP_R_EXIT (way out)}
   const float4 *program;
@@ -104,8 +105,6 @@ struct RenderArgs {
   uint32_t tiles_x, tile_shift; // tiles per row of tiles; log2 of the tile width (tile = 2^s x 2^(5-s) pixels)
   uint32_t scatter_mul;         // 0: slots in tile order; else slot -> slot * scatter_mul mod slots_per_chunk (coprime: a
                                 // permutation), so items claimed together are pixels far apart (scenes bound by slow pixels)
-  uint32_t scatter_tile_mul;    // 0: tiles in row-major order; else tile -> tile * mul mod tile count: the 32 pixels of a tile
-                                // stay together (coherent warps), consecutive tiles are far apart (no heavy region left for the end)
   int32_t first_row;            // first_pixel / img_width
   int32_t band_rows, band_period, band_phase;   // band_rows > 0: row y of the rendered set is image row
                                 // ((y / band_rows) * band_period + band_phase) * band_rows + y % band_rows (interleaved bands)
@@ -121,6 +120,7 @@ struct RenderArgs {
   uint32_t resume;               // chunk 0 starts from the sums already in `pixels` (progressive accumulation)
   uint32_t count_rays;
   uint32_t count_ops;            // run the instrumented kernel variant (per-ray operation counts for F_ray)
+  int32_t blocks_per_sm_cap;     // host only: launch at most this many blocks per SM (0 = as many as fit)
 };
 
 constexpr int STACK_CAPACITY = 32;     // traversal stack entries per thread (shared memory, [slot][thread])

@@ -41,8 +41,9 @@ constexpr int RT_MIN_BLOCKS_FAST = RT_MIN_BLOCKS_PER_SM, RT_MIN_BLOCKS_REF = RT_
 #else
 constexpr int RT_MIN_BLOCKS_FAST = 6, RT_MIN_BLOCKS_REF = 5;
 #endif
+// the stackless walk needs no shared memory and fits 80 registers: 6 blocks (Cornell box 377 -> 345 ms against 5 x 96)
 #ifndef RT_MIN_BLOCKS_LINEAR
-#define RT_MIN_BLOCKS_LINEAR 5
+#define RT_MIN_BLOCKS_LINEAR 6
 #endif
 constexpr int min_blocks(int mode) { return mode == 1 ? RT_MIN_BLOCKS_FAST : (mode == 3 ? RT_MIN_BLOCKS_LINEAR : RT_MIN_BLOCKS_REF); }
 
@@ -67,6 +68,7 @@ __device__ __forceinline__ bool trace(const Scene &sc, Ray &r, Hit &h, uint32_t 
   const float inf = __uint_as_float(0x7f800000u);
   if (MODE == 0) return rtt::trace_reference<false>(sc, r, 0.001f, inf, h, stk, stride, cnt);
   if (MODE == 2) return rtt::trace_reference<true>(sc, r, 0.001f, inf, h, stk, stride, cnt);   // reference order + treelets
+  if (MODE == 3) return rtt::trace_linear(sc, r, 0.001f, inf, h, cnt);                          // reference order, stackless
   return rtt::trace_fast(sc, r, 0.001f, inf, h, stk, stride, cnt);
 }
 
@@ -147,9 +149,7 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
           // scattered order: a warp's pixels come from all over the image, so the pixels with the long paths (which
           // bound a small image: their samples are produced in sequence) do not sit in the same warps
           if (a.scatter_mul) slot = (uint32_t)(((unsigned long long)slot * a.scatter_mul) % a.slots_per_chunk);
-          uint32_t tile = slot >> 5;
-          const uint32_t l = slot & 31u;
-          if (a.scatter_tile_mul) tile = (uint32_t)(((unsigned long long)tile * a.scatter_tile_mul) % (a.slots_per_chunk >> 5));
+          const uint32_t tile = slot >> 5, l = slot & 31u;
           const uint32_t ty = tile / a.tiles_x, tx = tile - ty * a.tiles_x;
           const uint32_t x = (tx << a.tile_shift) + (l & ((1u << a.tile_shift) - 1u)), y = (ty << (5u - a.tile_shift)) + (l >> a.tile_shift);
           if (x < (uint32_t)a.img_width && y * (uint32_t)a.img_width + x < (uint32_t)a.pixel_count) {
@@ -207,18 +207,10 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
     bool done = live && (budget <= 0);
     bool noise_pending = false;                           // this bounce's attenuation is a Perlin texture, evaluated below
     V3 noise_p = cam; float noise_scale = 0.0f;
-    Hit hl; bool hit_l = false;                           // MODE 3: the whole warp walks the scene's program together
-    if (MODE == 3) {
-      hl.u = 0.0f; hl.v = 0.0f; hl.t = 0.0f; hl.prim = 0; hl.front = 0; hl.p = cam; hl.n = cam;
-      hit_l = rtt::trace_linear(sc, ray, 0.001f, __uint_as_float(0x7f800000u), hl, live && !done, cnt);
-    }
     if (live && !done) {
       ++rays;
       Hit h; h.u = 0.0f; h.v = 0.0f; h.t = 0.0f; h.prim = 0; h.front = 0; h.p = cam; h.n = cam;
-      bool hit_any;
-      if (MODE == 3) { h = hl; hit_any = hit_l; }
-      else hit_any = trace<MODE>(sc, ray, h, stk, stride, cnt);
-      if (hit_any) {
+      if (trace<MODE>(sc, ray, h, stk, stride, cnt)) {
         const uint4 m0 = __ldg(sc.materials + 2 * h.prim);
         if (COUNT) {
           const uint32_t ty = m0.x & 0xffu, tk = (m0.x >> 8) & 0xffu;
@@ -408,17 +400,16 @@ __global__ void __launch_bounds__(PROBE_BLOCK) probe_trace_kernel(const Scene sc
                                                                   float tmin, float tmax, rt_probe_hit *__restrict__ out) {
   extern __shared__ __align__(16) uint32_t smem[];
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (MODE != 3 && i >= n) return;                        // the linear walk is a whole-warp job: idle lanes stay for the votes
-  const uint64_t j = i < n ? i : n - 1;
+  if (i >= n) return;
   Ray r;
-  r.o = v3(org[3 * j], org[3 * j + 1], org[3 * j + 2]);
-  r.d = v3(dir[3 * j], dir[3 * j + 1], dir[3 * j + 2]);
-  r.time = times ? times[j] : 0.0f;
+  r.o = v3(org[3 * i], org[3 * i + 1], org[3 * i + 2]);
+  r.d = v3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]);
+  r.time = times ? times[i] : 0.0f;
   Hit h; h.u = 0.0f; h.v = 0.0f; h.t = 0.0f; h.prim = 0; h.front = 0; h.p = v3(0, 0, 0); h.n = v3(0, 0, 0);
   bool hit;
   rtt::NoCount cnt;
   if (MODE == 0) hit = rtt::trace_reference<true>(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
-  else if (MODE == 3) { hit = rtt::trace_linear(sc, r, tmin, tmax, h, i < n, cnt); if (i >= n) return; }
+  else if (MODE == 3) hit = rtt::trace_linear(sc, r, tmin, tmax, h, cnt);
   else hit = rtt::trace_fast(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
   rt_probe_hit o;
   o.origin[0] = r.o.x; o.origin[1] = r.o.y; o.origin[2] = r.o.z;
@@ -514,6 +505,11 @@ static cudaError_t launch_render_t(const RenderArgs &args, int sm_count, cudaStr
   int per_sm = 0;
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, RT_BLOCK, smem);
   if (e != cudaSuccess) return e;
+  if (args.blocks_per_sm_cap > 0 && args.blocks_per_sm_cap < per_sm) per_sm = args.blocks_per_sm_cap;
+  if (const char *env = getenv("RT_BLOCKS_PER_SM")) {      // tuning knob: fewer resident blocks than fit
+    const long x = strtol(env, nullptr, 10);
+    if (x >= 1 && x < per_sm) per_sm = (int)x;
+  }
   if (per_sm < 1) per_sm = 1;
   long long want = ((long long)args.pixel_count + RT_BLOCK - 1) / RT_BLOCK;
   long long grid = (long long)sm_count * per_sm;

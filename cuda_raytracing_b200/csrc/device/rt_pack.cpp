@@ -358,8 +358,12 @@ struct Packer {
     const rt_hittable &h = H(href);
     const uint32_t inside = (in_t || in_r) ? 0x100u : 0u;
     switch (h.type) {
-      case RT_OBJ_SPHERE: case RT_OBJ_TRIANGLE: case RT_OBJ_QUAD:
+      case RT_OBJ_SPHERE:
         program_op(f4(0, 0, 0, 0), 0, 0, ref_index(tag[href]), ref_kind(tag[href]) | inside);
+        ++out.program_prims;
+        return true;
+      case RT_OBJ_TRIANGLE: case RT_OBJ_QUAD:                  // the plane (first word of the record) rides in the op
+        program_op(out.planars[4 * (size_t)ref_index(tag[href])], 0, 0, ref_index(tag[href]), ref_kind(tag[href]) | inside);
         ++out.program_prims;
         return true;
       case RT_OBJ_BVH_NODE: {

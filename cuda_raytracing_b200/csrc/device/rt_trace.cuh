@@ -121,10 +121,10 @@ __device__ __forceinline__ bool planar_inside(const Scene &sc, uint32_t idx, boo
   const float4 p3 = ldg4(sc.planars + 4 * idx + 3);        // u, w.z
   return planar_inside_rec(p1, p2, p3, triangle, r, t, p, alpha, beta);
 }
+// `p0` = first word of the record (normal, d): the linear program carries it inside the op, the other walks load it here
 template <bool EAGER = false>
-__device__ __forceinline__ bool planar_t(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float tmin, float tmax,
-                                         float &t_out) {
-  const float4 p0 = ldg4(sc.planars + 4 * idx);            // normal, d
+__device__ __forceinline__ bool planar_t_p0(const Scene &sc, const float4 p0, uint32_t idx, bool triangle, const Ray &r, float tmin,
+                                            float tmax, float &t_out) {
   float4 p1 = p0, p2 = p0, p3 = p0;
   if (EAGER) { p1 = ldg4(sc.planars + 4 * idx + 1); p2 = ldg4(sc.planars + 4 * idx + 2); p3 = ldg4(sc.planars + 4 * idx + 3); }
   const V3 n = v3(p0.x, p0.y, p0.z);
@@ -138,8 +138,12 @@ __device__ __forceinline__ bool planar_t(const Scene &sc, uint32_t idx, bool tri
   t_out = t;
   return true;
 }
-__device__ __forceinline__ void planar_record(const Scene &sc, uint32_t idx, const Ray &r, float t, Hit &h) {
-  const float4 p0 = ldg4(sc.planars + 4 * idx);
+template <bool EAGER = false>
+__device__ __forceinline__ bool planar_t(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float tmin, float tmax,
+                                         float &t_out) {
+  return planar_t_p0<EAGER>(sc, ldg4(sc.planars + 4 * idx), idx, triangle, r, tmin, tmax, t_out);
+}
+__device__ __forceinline__ void planar_record_p0(const Scene &sc, const float4 p0, uint32_t idx, const Ray &r, float t, Hit &h) {
   const V3 n = v3(p0.x, p0.y, p0.z);
   const float denom = dot_yfirst(n, r.d);
   float alpha, beta;
@@ -149,12 +153,24 @@ __device__ __forceinline__ void planar_record(const Scene &sc, uint32_t idx, con
   h.n = h.front ? n : vneg(n);
   h.prim = sc.sphere_count + idx;
 }
+__device__ __forceinline__ void planar_record(const Scene &sc, uint32_t idx, const Ray &r, float t, Hit &h) {
+  planar_record_p0(sc, ldg4(sc.planars + 4 * idx), idx, r, t, h);
+}
 template <bool EAGER = false>
 __device__ __forceinline__ bool hit_planar(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float tmin, float &tmax,
                                            Hit &h) {
   float t;
   if (!planar_t<EAGER>(sc, idx, triangle, r, tmin, tmax, t)) return false;
   planar_record(sc, idx, r, t, h);
+  tmax = t;
+  return true;
+}
+template <bool EAGER = false>
+__device__ __forceinline__ bool hit_planar_p0(const Scene &sc, const float4 p0, uint32_t idx, bool triangle, const Ray &r, float tmin,
+                                              float &tmax, Hit &h) {
+  float t;
+  if (!planar_t_p0<EAGER>(sc, p0, idx, triangle, r, tmin, tmax, t)) return false;
+  planar_record_p0(sc, p0, idx, r, t, h);
   tmax = t;
   return true;
 }
@@ -401,91 +417,80 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
 // The reference's walk has a FIXED visiting order: a BVH node pushes right then left, a structure its children in order,
 // a wrapper itself (the way out) and its child; nothing depends on the ray except WHETHER a node's box is entered.  The
 // packer therefore lays the whole walk out as a program (rt_device.h, Scene::program): op i is followed by op i + 1,
-// except that a box that is missed continues at its `skip` op (the first op after its subtree).  No stack.
-// All 32 lanes of a warp run the program together: each step executes the LOWEST op any lane still has to do
-// (redux.sync min), for the lanes that are at it.  The op is warp-uniform, so its kind is a uniform branch and its
-// record a broadcast load, and an op is issued at most once per warp and ray -- where the stack walk issues it once
-// per group of lanes that reach it at the same time.  Per lane the operations and their order are those of
-// trace_reference<false> (same helpers, same roundings, same drift of the ray through the wrappers).
-// Must be called by all 32 lanes; lanes with active == false only take part in the votes.
+// except that a box that is missed continues at its `skip` op (the first op after its subtree).  No stack: no pops, no
+// pushes, a structure costs nothing (its children simply follow), a wrapper is two ops (way in, way out) whose record
+// sits in the op, and so do a box's bounds and a quad's plane -- the first test of an op needs no second load.
+// Per lane the operations and their order are those of trace_reference<false> (same helpers, same roundings, same
+// drift of the ray through the wrappers); lanes meet by kind of op, as in the stack walk.
+// Measured (profiles/r1_linear_program.md): Cornell box s1024 406 -> 345 ms, scene 0 1.17 -> 1.11 ms, bit-identical.
+// A variant that walked the program in lockstep (every step the lowest op any lane has to do, redux.sync min; each op
+// issued once per warp and ray) ran 14 % SLOWER than the stack walk: 7 % fewer warp-instructions, but every step a
+// serial chain vote -> op load -> branch -> test, and the lanes' inside tests no longer overlap across quads.
 constexpr uint32_t OP_T_EXIT = 6u, OP_R_EXIT = 7u, OP_IN_WRAPPER = 0x100u;
 template <class C>
-__device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin, float tmax, Hit &h, const bool active, C &cnt) {
+__device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin, float tmax, Hit &h, C &cnt) {
   bool result = false, was_last_hit = false;
   V3 inv = v3(frcp(r.d.x), frcp(r.d.y), frcp(r.d.z));
   float a = dot_xfirst(r.d, r.d);
   const uint32_t n_ops = sc.program_ops;
-  uint32_t pc = active ? 0u : 0xffffffffu;
-  for (;;) {
-    const uint32_t cur = __reduce_min_sync(0xffffffffu, pc);
-    if (cur >= n_ops) break;
-    const float4 w0 = ldg4(sc.program + 2 * cur), w1 = ldg4(sc.program + 2 * cur + 1);
+  uint32_t pc = 0;
+  while (pc < n_ops) {
+    const float4 w0 = ldg4(sc.program + 2 * pc), w1 = ldg4(sc.program + 2 * pc + 1);
     const uint32_t code = __float_as_uint(w1.w), arg = __float_as_uint(w1.z);
-    const bool me = pc == cur;
-    if (me) pc = cur + 1u;
+    ++pc;
     switch (code & 7u) {
       case rtd::K_SPHERE:
-        if (me) {
-          cnt.sphere();
-          if (hit_sphere(sc, arg, r, a, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
-        }
+        cnt.sphere();
+        if (hit_sphere(sc, arg, r, a, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
         break;
       case rtd::K_TRIANGLE:
       case rtd::K_QUAD:
-        if (me) {
-          cnt.planar();
-          if (hit_planar<true>(sc, arg, (code & 7u) == rtd::K_TRIANGLE, r, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
-        }
+        cnt.planar();
+        if (hit_planar_p0(sc, w0, arg, (code & 7u) == rtd::K_TRIANGLE, r, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
         break;
-      case rtd::K_BVH:
-        if (me) {
-          float t0 = tmin, t1 = tmax;
-          cnt.box(1);
-          const bool ax = aabb_axis(w0.x, w0.y, r.o.x, inv.x, t0, t1);
-          const bool ay = aabb_axis(w0.z, w0.w, r.o.y, inv.y, t0, t1);
-          const bool az = aabb_axis(w1.x, w1.y, r.o.z, inv.z, t0, t1);
-          if (!(ax & ay & az)) pc = arg;
-        }
-        break;
+      case rtd::K_BVH: {
+        float t0 = tmin, t1 = tmax;
+        cnt.box(1);
+        const bool ax = aabb_axis(w0.x, w0.y, r.o.x, inv.x, t0, t1);
+        const bool ay = aabb_axis(w0.z, w0.w, r.o.y, inv.y, t0, t1);
+        const bool az = aabb_axis(w1.x, w1.y, r.o.z, inv.z, t0, t1);
+        if (!(ax & ay & az)) pc = arg;
+      } break;
       case rtd::K_TRANSLATION:
-        if (me) { cnt.translation(); was_last_hit = false; r.o = vsub(r.o, v3(w0.x, w0.y, w0.z)); }
+        cnt.translation();
+        was_last_hit = false;
+        r.o = vsub(r.o, v3(w0.x, w0.y, w0.z));
         break;
-      case OP_T_EXIT:
-        if (me) {
-          const V3 off = v3(w0.x, w0.y, w0.z);
-          cnt.translation();
-          r.o = vadd(r.o, off);
-          if (was_last_hit) h.p = vadd(h.p, off);
+      case OP_T_EXIT: {
+        const V3 off = v3(w0.x, w0.y, w0.z);
+        cnt.translation();
+        r.o = vadd(r.o, off);
+        if (was_last_hit) h.p = vadd(h.p, off);
+      } break;
+      case rtd::K_YROTATION: {                              // rt.cu:1194-1209, roundings from the reference's SASS
+        const float sn = w0.x, cs = w0.y;
+        cnt.rotation();
+        was_last_hit = false;
+        const V3 o = r.o, d = r.d;
+        r.o = v3(ffma(o.x, cs, -fmul(o.z, sn)), o.y, ffma(o.x, sn, fmul(o.z, cs)));
+        r.d = v3(ffma(d.x, cs, -fmul(d.z, sn)), d.y, ffma(d.z, cs, fmul(d.x, sn)));
+        inv.x = frcp(r.d.x); inv.z = frcp(r.d.z);
+        a = dot_xfirst(r.d, r.d);
+      } break;
+      default: {                                            // OP_R_EXIT, rt.cu:1210-1236
+        const float sn = w0.x, cs = w0.y;
+        cnt.rotation();
+        const V3 o = r.o, d = r.d;
+        r.o = v3(ffma(o.x, cs, fmul(o.z, sn)), o.y, ffma(o.z, cs, -fmul(o.x, sn)));
+        r.d = v3(ffma(d.x, cs, fmul(d.z, sn)), d.y, ffma(d.z, cs, -fmul(d.x, sn)));
+        if (was_last_hit) {
+          const V3 p = h.p, n = h.n;
+          h.p = v3(ffma(p.x, cs, fmul(p.z, sn)), p.y, ffma(p.z, cs, -fmul(p.x, sn)));
+          h.n = v3(ffma(n.x, cs, fmul(n.z, sn)), n.y, ffma(n.z, cs, -fmul(n.x, sn)));
         }
-        break;
-      case rtd::K_YROTATION:
-        if (me) {                                           // rt.cu:1194-1209, roundings from the reference's SASS
-          const float sn = w0.x, cs = w0.y;
-          cnt.rotation();
-          was_last_hit = false;
-          const V3 o = r.o, d = r.d;
-          r.o = v3(ffma(o.x, cs, -fmul(o.z, sn)), o.y, ffma(o.x, sn, fmul(o.z, cs)));
-          r.d = v3(ffma(d.x, cs, -fmul(d.z, sn)), d.y, ffma(d.z, cs, fmul(d.x, sn)));
-          inv.x = frcp(r.d.x); inv.z = frcp(r.d.z);
-          a = dot_xfirst(r.d, r.d);
-        }
-        break;
-      default:                                              // OP_R_EXIT, rt.cu:1210-1236
-        if (me) {
-          const float sn = w0.x, cs = w0.y;
-          cnt.rotation();
-          const V3 o = r.o, d = r.d;
-          r.o = v3(ffma(o.x, cs, fmul(o.z, sn)), o.y, ffma(o.z, cs, -fmul(o.x, sn)));
-          r.d = v3(ffma(d.x, cs, fmul(d.z, sn)), d.y, ffma(d.z, cs, -fmul(d.x, sn)));
-          if (was_last_hit) {
-            const V3 p = h.p, n = h.n;
-            h.p = v3(ffma(p.x, cs, fmul(p.z, sn)), p.y, ffma(p.z, cs, -fmul(p.x, sn)));
-            h.n = v3(ffma(n.x, cs, fmul(n.z, sn)), n.y, ffma(n.z, cs, -fmul(n.x, sn)));
-          }
-          inv.x = frcp(r.d.x); inv.z = frcp(r.d.z);
-          a = dot_xfirst(r.d, r.d);
-        }
-        break;
+        inv.x = frcp(r.d.x); inv.z = frcp(r.d.z);
+        a = dot_xfirst(r.d, r.d);
+      } break;
     }
   }
   return result;

@@ -333,8 +333,8 @@ def test_hybrid_walk_equals_reference_order(product_lib, sid):
     saved = {k: os.environ.get(k) for k in ("RT_FUSE_MIN", "RT_TREELET_MIN", "RT_LINEAR")}
     results = []
     try:
-        # the literal stack walk; the hybrid walk forced two ways; the automatic choice (small scenes: the linear program
-        # walked by whole warps, kernel mode 3); the automatic choice without the linear program
+        # the literal stack walk; the hybrid walk forced two ways; the automatic choice (small scenes: the stackless linear
+        # program, kernel mode 3); the automatic choice without the linear program
         for knobs, trav in (({}, product_lib.RT_TRAVERSAL_REFERENCE), ({"RT_FUSE_MIN": "1", "RT_TREELET_MIN": "2"}, product_lib.RT_TRAVERSAL_AUTO),
                             ({"RT_FUSE_MIN": "0", "RT_TREELET_MIN": "3"}, product_lib.RT_TRAVERSAL_AUTO),
                             ({}, product_lib.RT_TRAVERSAL_AUTO), ({"RT_LINEAR": "0"}, product_lib.RT_TRAVERSAL_AUTO)):
