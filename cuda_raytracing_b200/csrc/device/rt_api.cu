@@ -309,8 +309,10 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   a.pixels = d_pixels;
   a.rng_states = (uint32_t *)ctx->b_rng_states.ptr;
   a.progress = (uint32_t *)ctx->b_progress.ptr;
-  const int mode = kernel_mode(ctx->packed);
-  const double lanes = (double)ctx->sm_count * ((mode == 1 || mode == 3) ? 768.0 : 640.0);   // resident threads: 6 or 5 blocks of 128 per SM
+  int mode = kernel_mode(ctx->packed);
+  // short-lived pixels (the regime that gets no time slices either) on the stackless walk: the 5 x 96-register build
+  if (mode == 3 && p->max_bounces <= 64 && (long long)p->samples_per_pixel * (long long)(p->max_bounces > 0 ? p->max_bounces : 1) <= 256) mode = 4;
+  const double lanes = (double)ctx->sm_count * (mode == 3 ? 1024.0 : (mode == 1 ? 768.0 : 640.0));   // resident threads: 8, 6 or 5 blocks of 128 per SM
   {   // chunk size: about 1/32 of the samples one resident lane will produce, so that the tail of the render (lanes
       // idle because every remaining pixel is owned) is a few per cent; never below 8 samples per claim
     const int spp = p->samples_per_pixel > 0 ? p->samples_per_pixel : 1;
@@ -373,11 +375,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   a.resume = resume ? 1u : 0u;
   a.count_rays = (p->flags & (RT_RENDER_COUNT_RAYS | RT_RENDER_COUNT_OPS)) ? 1u : 0u;
   a.count_ops = (p->flags & RT_RENDER_COUNT_OPS) ? 1u : 0u;
-  if (mode == 3) {
-    a.stack_entries = 0;                                   // the linear program needs no traversal stack
-    // short-lived pixels (the regime that gets no time slices either): 5 resident blocks beat 6 (scene 0, s16 b8: 1.13 vs 1.18 ms)
-    if ((long long)a.samples_per_pixel * (long long)(p->max_bounces > 0 ? p->max_bounces : 1) <= 256) a.blocks_per_sm_cap = 5;
-  }
+  if (mode >= 3) a.stack_entries = 0;                      // the linear program needs no traversal stack
   RT_CUDA(ctx, rtk::launch_render(a, mode, ctx->sm_count, s, &ctx->last_launch));
   ++launches;
   if (stats) {

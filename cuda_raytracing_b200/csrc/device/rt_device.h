@@ -120,7 +120,6 @@ struct RenderArgs {
   uint32_t resume;               // chunk 0 starts from the sums already in `pixels` (progressive accumulation)
   uint32_t count_rays;
   uint32_t count_ops;            // run the instrumented kernel variant (per-ray operation counts for F_ray)
-  int32_t blocks_per_sm_cap;     // host only: launch at most this many blocks per SM (0 = as many as fit)
 };
 
 constexpr int STACK_CAPACITY = 32;     // traversal stack entries per thread (shared memory, [slot][thread])

@@ -41,9 +41,12 @@ constexpr int RT_MIN_BLOCKS_FAST = RT_MIN_BLOCKS_PER_SM, RT_MIN_BLOCKS_REF = RT_
 #else
 constexpr int RT_MIN_BLOCKS_FAST = 6, RT_MIN_BLOCKS_REF = 5;
 #endif
-// the stackless walk needs no shared memory and fits 80 registers: 6 blocks (Cornell box 377 -> 345 ms against 5 x 96)
+// the stackless walk (modes 3 and 4) needs no shared memory and gains from residency: Cornell box s1024 377 ms at 5 x 96
+// registers, 345 at 6 x 80, 337 at 7 x 72, 327 at 8 x 64, 361 at 10 x 48 (profiles/r1b_linear_program_knobs.jsonl).  Short-
+// lived pixels (scene 0, s16 b8) want the opposite -- 1.11 ms at 5 x 96, 1.18 at 8 x 64 resident -- and get mode 4.
+// The stack walks lose at 7 or 8 blocks (C2 95 -> 103 ms, C3 27 -> 33, scene 3 unchanged).
 #ifndef RT_MIN_BLOCKS_LINEAR
-#define RT_MIN_BLOCKS_LINEAR 6
+#define RT_MIN_BLOCKS_LINEAR 8
 #endif
 constexpr int min_blocks(int mode) { return mode == 1 ? RT_MIN_BLOCKS_FAST : (mode == 3 ? RT_MIN_BLOCKS_LINEAR : RT_MIN_BLOCKS_REF); }
 
@@ -68,7 +71,7 @@ __device__ __forceinline__ bool trace(const Scene &sc, Ray &r, Hit &h, uint32_t 
   const float inf = __uint_as_float(0x7f800000u);
   if (MODE == 0) return rtt::trace_reference<false>(sc, r, 0.001f, inf, h, stk, stride, cnt);
   if (MODE == 2) return rtt::trace_reference<true>(sc, r, 0.001f, inf, h, stk, stride, cnt);   // reference order + treelets
-  if (MODE == 3) return rtt::trace_linear(sc, r, 0.001f, inf, h, cnt);                          // reference order, stackless
+  if (MODE >= 3) return rtt::trace_linear(sc, r, 0.001f, inf, h, cnt);                          // reference order, stackless
   return rtt::trace_fast(sc, r, 0.001f, inf, h, stk, stride, cnt);
 }
 
@@ -505,7 +508,6 @@ static cudaError_t launch_render_t(const RenderArgs &args, int sm_count, cudaStr
   int per_sm = 0;
   e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, RT_BLOCK, smem);
   if (e != cudaSuccess) return e;
-  if (args.blocks_per_sm_cap > 0 && args.blocks_per_sm_cap < per_sm) per_sm = args.blocks_per_sm_cap;
   if (const char *env = getenv("RT_BLOCKS_PER_SM")) {      // tuning knob: fewer resident blocks than fit
     const long x = strtol(env, nullptr, 10);
     if (x >= 1 && x < per_sm) per_sm = (int)x;
@@ -529,12 +531,13 @@ cudaError_t launch_render(const rtd::RenderArgs &args, int mode, int sm_count, c
   if (args.count_ops) {                                  // instrumented build of the same kernel (not the timed one)
     if (mode == 0) return launch_render_t<0, 256, true>(args, sm_count, stream, info);
     if (mode == 2) return launch_render_t<2, 256, true>(args, sm_count, stream, info);
-    if (mode == 3) return launch_render_t<3, 256, true>(args, sm_count, stream, info);
+    if (mode >= 3) return launch_render_t<3, 256, true>(args, sm_count, stream, info);
     return launch_render_t<1, 256, true>(args, sm_count, stream, info);
   }
   if (mode == 0) return small ? launch_render_t<0, 64, false>(args, sm_count, stream, info) : launch_render_t<0, 256, false>(args, sm_count, stream, info);
   if (mode == 2) return small ? launch_render_t<2, 64, false>(args, sm_count, stream, info) : launch_render_t<2, 256, false>(args, sm_count, stream, info);
-  if (mode == 3) return small ? launch_render_t<3, 64, false>(args, sm_count, stream, info) : launch_render_t<3, 256, false>(args, sm_count, stream, info);
+  if (mode == 4 && small) return launch_render_t<4, 64, false>(args, sm_count, stream, info);   // mode 3 at 5 x 96 registers
+  if (mode >= 3) return small ? launch_render_t<3, 64, false>(args, sm_count, stream, info) : launch_render_t<3, 256, false>(args, sm_count, stream, info);
   return small ? launch_render_t<1, 64, false>(args, sm_count, stream, info) : launch_render_t<1, 256, false>(args, sm_count, stream, info);
 }
 
