@@ -94,7 +94,7 @@ EXPORTS = [
     "rt_context_create", "rt_context_destroy", "rt_last_error_string", "rt_context_set_stream", "rt_context_reset_stream", "rt_scene_upload",
     "rt_render_params_from_camera", "rt_render_device", "rt_resolve_device", "rt_render", "rt_synchronize",
     "rt_render_state_save", "rt_render_state_load",
-    "rt_scene_pack_info", "rt_render_world", "rt_probe_trace", "rt_probe_scatter", "rt_probe_texture", "rt_probe_xorwow",
+    "rt_scene_pack_info", "rt_scene_program", "rt_render_world", "rt_probe_trace", "rt_probe_scatter", "rt_probe_texture", "rt_probe_xorwow",
     # rt_scene.h
     "rt_world_init", "rt_world_free", "rt_mat_lambert_solid", "rt_mat_light_solid", "rt_mat_lambert_image",
     "rt_mat_lambert_image_pixels",
@@ -130,6 +130,7 @@ def lib():
         L.rt_render.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.POINTER(Stats)]
         L.rt_synchronize.argtypes = [C.c_void_p]
         L.rt_scene_pack_info.argtypes = [C.POINTER(SceneDesc), C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(PackInfo)]
+        L.rt_scene_program.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]
         L.rt_render_state_save.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.rt_render_state_load.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_uint64]
         L.rt_render_world.argtypes = [C.c_void_p, C.POINTER(World), C.POINTER(RenderSettings), C.c_uint32, C.c_void_p,
@@ -250,6 +251,16 @@ class HostScene:
         if rc != 0:
             raise RtError("rt_scene_pack_info: %d %s" % (rc, (lib().rt_last_error_string(None) or b"").decode()))
         return info
+
+    def program(self):
+        """The linear program of the scene's reference-order walk (host only): uint32 view, shape (ops, 8); empty if none."""
+        d = self.desc()
+        n = C.c_uint32(0)
+        _check(lib().rt_scene_program(C.byref(d), None, 0, C.byref(n)))
+        ops = np.zeros((n.value, 8), dtype=np.uint32)
+        if n.value:
+            _check(lib().rt_scene_program(C.byref(d), ops.ctypes.data, n.value, C.byref(n)))
+        return ops
 
     def close(self):
         if self.world.hittables:

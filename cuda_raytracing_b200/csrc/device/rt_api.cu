@@ -564,6 +564,17 @@ int rt_scene_pack_info(const rt_scene_desc *scene, uint32_t traversal, uint32_t 
   return RT_OK;
 }
 
+int rt_scene_program(const rt_scene_desc *scene, float *ops8_out, uint32_t capacity_ops, uint32_t *n_ops_out) {
+  if (!scene || !n_ops_out || (capacity_ops > 0 && !ops8_out)) return fail(nullptr, RT_ERR_INVALID, "rt_scene_program: NULL argument");
+  rtp::PackedScene p;
+  const int rc = rtp::pack_scene(*scene, RT_TRAVERSAL_AUTO, p);
+  if (rc != RT_OK) return fail(nullptr, rc, p.error);
+  const uint32_t n = kernel_mode(p) == 3 ? (uint32_t)(p.program.size() / 2) : 0u;
+  *n_ops_out = n;
+  if (n > 0 && capacity_ops > 0) memcpy(ops8_out, p.program.data(), sizeof(float) * 8 * (size_t)std::min(n, capacity_ops));
+  return RT_OK;
+}
+
 int rt_probe_xorwow(rt_context *ctx, uint64_t seed, uint64_t first_subsequence, uint64_t n, uint32_t *states6_out) {
   if (!ctx || !states6_out) return fail(ctx, RT_ERR_INVALID, "rt_probe_xorwow: NULL argument");
   RT_CUDA(ctx, cudaSetDevice(ctx->device));

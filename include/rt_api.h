@@ -156,6 +156,15 @@ typedef struct rt_pack_info {
 } rt_pack_info;
 int rt_scene_pack_info(const rt_scene_desc *scene, uint32_t traversal, uint32_t treelet_min, uint32_t fuse_min, rt_pack_info *out);
 
+/* The linear program RT_TRAVERSAL_AUTO would upload for `scene` (host only, no GPU needed), for inspection and tests:
+ * 8 floats per op -- {x0,x1,y0,y1, z0,z1, skip op, K_BVH} for a box (a missed box continues at `skip`, every other op at
+ * the next one), {plane n.xyz,d | 0, 0,0, primitive index, kind | 0x100 inside a wrapper} for a primitive (kind: 0 sphere,
+ * 2 triangle, 3 quad; the index counts spheres, or quads and triangles together, in the order of the hittable array),
+ * {offset.xyz,0, 0,0,0, 4 way in | 6 way out} for a translation, {sin,cos,0,0, 0,0,0, 5 | 7} for a y-rotation; the last
+ * two words of an op are raw 32-bit integers.  *n_ops_out = ops of the program (0: the scene has none); at most
+ * capacity_ops ops are written to ops8_out (may be NULL with capacity 0). */
+int rt_scene_program(const rt_scene_desc *scene, float *ops8_out, uint32_t capacity_ops, uint32_t *n_ops_out);
+
 #ifdef __cplusplus
 }
 #endif
