@@ -67,6 +67,7 @@ struct rt_context {
   uint32_t treelet_min = 8;                                // env RT_TREELET_MIN: smallest wrapper-free subtree given an own BVH (0 = none)
   int tile_w = 8;                                          // work items walk 8x4-pixel tiles; env RT_TILE_W (1..32, power of 2)
   int linear = -1;                                         // small scenes with wrappers walk their linear program (kernel mode 3): -1 / 1 yes, 0 never; env RT_LINEAR
+  int flat = -1;                                           // tiny scenes without wrappers skip their BVH (kernel mode 5): -1 / 1 yes, 0 never; env RT_FLAT
   int scatter = -1;                                        // item order: -1 automatic, 0 tile order, 1 scattered; env RT_SCATTER
   uint64_t rng_seed = 0, rng_first = 0, rng_count = 0, rng_bands = 0; bool rng_valid = false;   // what b_rng_init holds
   uint64_t live_seed = 0, live_first = 0, live_count = 0, live_bands = 0; bool live_valid = false;  // what b_rng_states carries on from
@@ -113,6 +114,7 @@ int rt_context_create(int device_id, rt_context **out) {
   if (const char *v = getenv("RT_FUSE_MIN")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 30)) ctx->fuse_min = (uint32_t)x; }
   if (const char *v = getenv("RT_TREELET_MIN")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 30)) ctx->treelet_min = (uint32_t)x; }
   if (const char *v = getenv("RT_LINEAR")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->linear = (int)x; }
+  if (const char *v = getenv("RT_FLAT")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->flat = (int)x; }
   if (const char *v = getenv("RT_SCATTER")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->scatter = (int)x; }
   if (const char *v = getenv("RT_CLAIM_GROUP")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= 32) ctx->claim_group = (int)x; }
   std::vector<uint32_t> mats;
@@ -167,6 +169,7 @@ int rt_scene_upload(rt_context *ctx, const rt_scene_desc *desc, uint32_t travers
   rtp::PackedScene &p = ctx->packed;
   int rc = rtp::pack_scene(*desc, traversal, p, ctx->treelet_min, ctx->fuse_min, ctx->linear == 0 ? 0u : rtp::PROGRAM_MAX_DEFAULT);
   if (rc != RT_OK) return fail(ctx, rc, p.error);
+  if (ctx->flat == 0) p.flat = false;
   cudaStream_t s = ctx->stream;
 #define UP(buf, vec) RT_CUDA(ctx, ctx->buf.upload((vec).data(), (vec).size() * sizeof((vec)[0]), s))
   UP(b_ref_nodes, p.ref_nodes); UP(b_xforms, p.xforms); UP(b_instances, p.instances); UP(b_structs, p.structures); UP(b_struct_children, p.struct_children);
@@ -182,7 +185,7 @@ int rt_scene_upload(rt_context *ctx, const rt_scene_desc *desc, uint32_t travers
   sc.program = (const float4 *)ctx->b_program.ptr; sc.program_ops = (uint32_t)(p.program.size() / 2);
   sc.ref_root = p.ref_root; sc.fast_nodes = (const float4 *)ctx->b_fast_nodes.ptr; sc.fast_root = p.fast_root;
   sc.spheres = (const float4 *)ctx->b_spheres.ptr; sc.planars = (const float4 *)ctx->b_planars.ptr;
-  sc.sphere_count = p.sphere_count; sc.planar_count = p.planar_count;
+  sc.sphere_count = p.sphere_count; sc.planar_count = p.planar_count; sc.flat_triangles = p.flat_triangles;
   sc.materials = (const uint4 *)ctx->b_materials.ptr; sc.checkers = (const float4 *)ctx->b_checkers.ptr;
   sc.perlin_vectors = (const float4 *)ctx->b_perlin_vec.ptr; sc.perlin_perm = (const uint8_t *)ctx->b_perlin_perm.ptr;
   sc.perlin_tables = p.perlin_tables; sc.tex_arena = (const uint8_t *)ctx->b_arena.ptr; sc.tex_bytes = p.tex_arena.size();
@@ -195,10 +198,10 @@ int rt_scene_upload(rt_context *ctx, const rt_scene_desc *desc, uint32_t travers
   return RT_OK;
 }
 
-// kernel variant: 1 = own BVH over the whole scene, 3 = reference order as a linear program (small scenes with wrappers),
+// kernel variant: 1 = own BVH over the whole scene, 5 = tiny scene without wrappers (every primitive, no BVH), 3 = reference order as a linear program (small scenes with wrappers),
 // 2 = reference order with treelets / fused instances, 0 = reference order through the stack
 static int kernel_mode(const rtp::PackedScene &p) {
-  if (p.traversal_used == RT_TRAVERSAL_FAST) return 1;
+  if (p.traversal_used == RT_TRAVERSAL_FAST) return p.flat ? 5 : 1;
   if (p.treelets + p.fused_instances > 0) return 2;
   return p.program.empty() ? 0 : 3;
 }
@@ -312,7 +315,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   int mode = kernel_mode(ctx->packed);
   // short-lived pixels (the regime that gets no time slices either) on the stackless walk: the 5 x 96-register build
   if (mode == 3 && p->max_bounces <= 64 && (long long)p->samples_per_pixel * (long long)(p->max_bounces > 0 ? p->max_bounces : 1) <= 256) mode = 4;
-  const double lanes = (double)ctx->sm_count * (mode == 3 ? 1024.0 : (mode == 1 ? 768.0 : 640.0));   // resident threads: 8, 6 or 5 blocks of 128 per SM
+  const double lanes = (double)ctx->sm_count * (mode == 3 ? 1024.0 : ((mode == 1 || mode == 5) ? 768.0 : 640.0));   // resident threads: 8, 6 or 5 blocks of 128 per SM
   {   // chunk size: about 1/32 of the samples one resident lane will produce, so that the tail of the render (lanes
       // idle because every remaining pixel is owned) is a few per cent; never below 8 samples per claim
     const int spp = p->samples_per_pixel > 0 ? p->samples_per_pixel : 1;
@@ -375,7 +378,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   a.resume = resume ? 1u : 0u;
   a.count_rays = (p->flags & (RT_RENDER_COUNT_RAYS | RT_RENDER_COUNT_OPS)) ? 1u : 0u;
   a.count_ops = (p->flags & RT_RENDER_COUNT_OPS) ? 1u : 0u;
-  if (mode >= 3) a.stack_entries = 0;                      // the linear program needs no traversal stack
+  if (mode >= 3) a.stack_entries = 0;                      // neither the linear program nor the tiny-scene walk needs a traversal stack
   RT_CUDA(ctx, rtk::launch_render(a, mode, ctx->sm_count, s, &ctx->last_launch));
   ++launches;
   if (stats) {

@@ -84,6 +84,7 @@ struct Scene {
   const float4 *spheres;        // 2 per sphere: {cx,cy,cz,r} {mx,my,mz, flags (bit0: needs uv)}
   const float4 *planars;        // 4 per quad/triangle: {n.xyz,d} {q.xyz,w.x} {v.xyz,w.y} {u.xyz,w.z}
   uint32_t sphere_count, planar_count;
+  uint32_t flat_triangles;      // trace_flat (tiny scenes, kernel mode 5): bit i set = planar i is a triangle
   // second primitive set for flattened instances (FAST mode on scenes with wrappers) lives in the same arrays
   const uint4 *materials;       // 2 x 16 B per primitive id
   const float4 *checkers;       // 2 per record: {inv_scale, even.rgb} {0, odd.rgb}

@@ -14,7 +14,8 @@ namespace rtk {
 struct LaunchInfo { int grid, block, regs, blocks_per_sm; size_t smem; };
 
 // mode: 0 = reference-order traversal, 1 = own BVH, 2 = reference order with own-BVH treelets, 3 = reference order as a
-// linear program, no stack (args.scene.program), 4 = the same for short-lived pixels (fewer resident blocks, more registers).  Enqueues on `stream`; *info (optional) describes the launch.
+// linear program, no stack (args.scene.program), 4 = the same for short-lived pixels (fewer resident blocks, more registers),
+// 5 = tiny scene without wrappers: every primitive tested, no BVH, no stack.  Enqueues on `stream`; *info (optional) describes the launch.
 cudaError_t launch_render(const rtd::RenderArgs &args, int mode, int sm_count, cudaStream_t stream, LaunchInfo *info);
 
 // XORWOW states {d,v0..v4} for subsequences first..first+n-1 of `seed`.

@@ -572,6 +572,15 @@ struct Packer {
       out.has_fast = true;
     }
     out.traversal_used = want_fast ? RT_TRAVERSAL_FAST : RT_TRAVERSAL_REFERENCE;
+    // tiny scenes without wrappers (so the primitive arrays are exactly the scene): no BVH at all
+    if (want_fast && !out.has_wrappers && out.spheres.size() / 2 <= 4 && out.planars.size() / 4 <= 4) {
+      out.flat = true;
+      uint32_t k = 0;
+      for (uint64_t i = 0; i < n; ++i) {
+        if (H((uint32_t)i).type == RT_OBJ_TRIANGLE) out.flat_triangles |= 1u << k;
+        if (H((uint32_t)i).type == RT_OBJ_TRIANGLE || H((uint32_t)i).type == RT_OBJ_QUAD) ++k;
+      }
+    }
     const uint32_t need = want_fast ? out.fast_stack_need : out.ref_stack_need;
     if (need > (uint32_t)STACK_CAPACITY) {
       out.error = "rt_scene_upload: traversal stack need " + std::to_string(need) + " exceeds device capacity " + std::to_string(STACK_CAPACITY);

@@ -24,6 +24,8 @@ struct PackedScene {
   uint32_t sphere_count = 0, planar_count = 0, perlin_tables = 0;
   bool has_wrappers = false;             // any translation / y-rotation in the scene
   bool has_fast = false;                 // fast_nodes valid
+  bool flat = false;                     // own-BVH scene of at most 4 spheres and 4 planars: walked without the BVH (trace_flat)
+  uint32_t flat_triangles = 0;           // bit i: planar i is a triangle
   uint32_t ref_stack_need = 0, fast_stack_need = 0;
   uint32_t treelets = 0, treelet_prims = 0;   // own-BVH stand-ins inside the reference graph
   uint32_t fused_instances = 0;               // wrapper chains around one primitive / structure done as one item

@@ -496,6 +496,72 @@ __device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin
   return result;
 }
 
+// ================= tiny scenes without wrappers: every primitive, no BVH, no stack ================================
+// Scenes of at most 4 spheres and 4 quads / triangles (the Perlin scenes 17 and 19 among them) are bound by the latency
+// of ONE lane: their slowest pixels are a serial chain of up to spp x 50 bounces (profiles/r1b_linear_program.md).  A BVH
+// saves them no work; it only adds a node test and a stack trip in front of sphere tests that then run one after the
+// other.  Here the spheres are tested two at a time in one basic block (independent sqrt / divisions interleave, see
+// rt_math.cuh) against the tmax the walk started with; the closest hit is then picked in primitive order.  That is
+// the result of testing them one after the other with a shrinking tmax: a sphere's candidate root does not depend on
+// tmax except through the final `root < tmax`, because root2 >= root1 (same divisor > 0), so a root1 that a smaller
+// tmax would reject is followed by a root2 that it rejects as well.
+__device__ __forceinline__ void sphere_stage(const Scene &sc, uint32_t idx, const Ray &r, float a, float &b, float &disc) {
+  const float4 s0 = ldg4(sc.spheres + 2 * idx);
+  const float4 s1 = ldg4(sc.spheres + 2 * idx + 1);
+  const V3 c = v3(ffma(r.time, s1.x, s0.x), ffma(r.time, s1.y, s0.y), ffma(r.time, s1.z, s0.z));   // movement_path_at
+  const V3 oc = vsub(c, r.o);
+  b = fmul(dot_yfirst(r.d, oc), -2.0f);
+  const float cc = ffma(-s0.w, s0.w, dot_yfirst(oc, oc));
+  disc = ffma(b, b, fmul(cc, fmul(a, -4.0f)));
+}
+// the two candidate roots of two spheres at once; returns false when a guard of the fast arithmetic fails (caller falls back)
+__device__ __forceinline__ bool sphere_roots2_fast(float b0, float disc0, float b1, float disc1, float a2, float tmin, float tmax,
+                                                   float &t0, bool &h0, float &t1, bool &h1) {
+  const bool v0 = disc0 >= 0.0f, v1 = disc1 >= 0.0f;               // a negative discriminant is a miss: its lane computes on 1.0
+  const float d0 = v0 ? disc0 : 1.0f, d1 = v1 ? disc1 : 1.0f;
+  if (!(fsqrt_fast_ok(d0) && fsqrt_fast_ok(d1))) return false;
+  const float q0 = fsqrt_fast(d0), q1 = fsqrt_fast(d1);
+  const float n00 = fsub(-b0, q0), n01 = fsub(q0, b0), n10 = fsub(-b1, q1), n11 = fsub(q1, b1);
+  if (!(fdiv_fast_ok(n00, a2) && fdiv_fast_ok(n01, a2) && fdiv_fast_ok(n10, a2) && fdiv_fast_ok(n11, a2))) return false;
+  const float r00 = fdiv_fast(n00, a2), r01 = fdiv_fast(n01, a2), r10 = fdiv_fast(n10, a2), r11 = fdiv_fast(n11, a2);
+  t0 = (tmin >= r00 || r00 >= tmax) ? r01 : r00;
+  t1 = (tmin >= r10 || r10 >= tmax) ? r11 : r10;
+  h0 = v0 && tmin < t0 && t0 < tmax;
+  h1 = v1 && tmin < t1 && t1 < tmax;
+  return true;
+}
+template <class C>
+__device__ __forceinline__ bool trace_flat(const Scene &sc, const Ray &r, float tmin, float tmax, Hit &h, C &cnt) {
+  const float a = dot_xfirst(r.d, r.d);
+  const float a2 = fadd(a, a);
+  const uint32_t ns = sc.sphere_count, np = sc.planar_count;
+  uint32_t best = 0xffffffffu;
+  float tbest = tmax;
+  for (uint32_t i = 0; i < ns; i += 2) {
+    const uint32_t j = (i + 1 < ns) ? i + 1 : i;                      // odd count: the last sphere stands in for its missing partner
+    float b0, disc0, b1, disc1, t0 = 0.0f, t1 = 0.0f;
+    bool h0 = false, h1 = false;
+    cnt.sphere(); if (j != i) cnt.sphere();
+    sphere_stage(sc, i, r, a, b0, disc0);
+    sphere_stage(sc, j, r, a, b1, disc1);
+    if (!sphere_roots2_fast(b0, disc0, b1, disc1, a2, tmin, tmax, t0, h0, t1, h1)) {   // rare: operands outside the guards
+      h0 = sphere_root(sc, i, r, a, tmin, tmax, t0);
+      h1 = sphere_root(sc, j, r, a, tmin, tmax, t1);
+    }
+    if (h0 && t0 < tbest) { tbest = t0; best = rtd::make_ref(rtd::K_SPHERE, i); }
+    if (j != i && h1 && t1 < tbest) { tbest = t1; best = rtd::make_ref(rtd::K_SPHERE, j); }
+  }
+  for (uint32_t i = 0; i < np; ++i) {
+    float tt;
+    cnt.planar();
+    if (planar_t(sc, i, (sc.flat_triangles >> i) & 1u, r, tmin, tbest, tt)) { tbest = tt; best = rtd::make_ref(rtd::K_QUAD, i); }
+  }
+  if (best == 0xffffffffu) return false;
+  if (rtd::ref_kind(best) == rtd::K_SPHERE) sphere_record(sc, rtd::ref_index(best), r, tbest, h);
+  else planar_record(sc, rtd::ref_index(best), r, tbest, h);
+  return true;
+}
+
 // ================= own BVH (SAH, world-space primitives, near child first) =====================================
 // Closest hit is independent of visiting order and of (conservative) box culling, so for scenes without
 // instance wrappers this returns bit-identical hits to trace_reference at a fraction of the node visits.

@@ -290,16 +290,17 @@ def test_tier2_converged_images_vs_reference_gpu(gpu_ctx, oracle, product_lib, s
 @pytest.mark.gpu
 @pytest.mark.parametrize("sid", [2, 17, 0])
 def test_image_does_not_depend_on_scheduling_knobs(product_lib, sid):
-    """Chunk size, tile shape, claim grouping and item order (tile order / scattered) only change WHO renders a
-    pixel's samples and when, never the samples: the image is bit-identical whatever the knobs (contexts read them
-    from the environment at creation).  Scene 17 is the one whose automatic choice is the scattered order."""
+    """Chunk size, tile shape, claim grouping, item order (tile order / scattered) and which of the exact walks a scene
+    gets only change WHO renders a pixel's samples, when and through which code, never the samples: the image is
+    bit-identical whatever the knobs (contexts read them from the environment at creation)."""
     hs = product_lib.HostScene(sid)
     p = hs.params(200, 24, 12)
     images = []
     knobs = [{}, {"RT_CHUNK": "5"}, {"RT_CHUNK": "1000000"}, {"RT_CHUNK": "7", "RT_TILE_W": "32", "RT_CLAIM_GROUP": "1"},
              {"RT_CHUNK": "3", "RT_TILE_W": "4", "RT_CLAIM_GROUP": "32"}, {"RT_SCATTER": "0"}, {"RT_SCATTER": "1"},
-             {"RT_SCATTER": "1", "RT_CHUNK": "4", "RT_TILE_W": "2", "RT_CLAIM_GROUP": "32"}]
-    saved = {k: os.environ.get(k) for k in ("RT_CHUNK", "RT_TILE_W", "RT_CLAIM_GROUP", "RT_SCATTER")}
+             {"RT_SCATTER": "1", "RT_CHUNK": "4", "RT_TILE_W": "2", "RT_CLAIM_GROUP": "32"},
+             {"RT_FLAT": "0"}, {"RT_LINEAR": "0"}]                 # scene 17 through its BVH, scene 0 through the stack walk
+    saved = {k: os.environ.get(k) for k in ("RT_CHUNK", "RT_TILE_W", "RT_CLAIM_GROUP", "RT_SCATTER", "RT_FLAT", "RT_LINEAR")}
     try:
         for kn in knobs:
             for k in saved:

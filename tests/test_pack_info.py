@@ -10,15 +10,16 @@ def test_every_scene_packs_in_every_mode(product_lib, sid):
         i = hs.pack_info(trav)
         assert 1 <= i.stack_need <= i.stack_capacity
         assert i.spheres + i.planars >= 1
+        tiny = not i.has_wrappers and i.spheres <= 4 and i.planars <= 4       # walked without its BVH (kernel mode 5)
         if trav == product_lib.RT_TRAVERSAL_FAST:
-            assert (i.traversal_used, i.kernel_mode) == (product_lib.RT_TRAVERSAL_FAST, 1) and i.own_nodes >= 1
+            assert (i.traversal_used, i.kernel_mode) == (product_lib.RT_TRAVERSAL_FAST, 5 if tiny else 1) and i.own_nodes >= 1
         if trav == product_lib.RT_TRAVERSAL_REFERENCE:          # the literal walk: no stand-ins
             assert (i.traversal_used, i.kernel_mode) == (product_lib.RT_TRAVERSAL_REFERENCE, 0)
             assert i.treelets == i.fused_instances == i.own_nodes == 0
             assert i.program_ops == 0
         if trav == product_lib.RT_TRAVERSAL_AUTO:               # exact results: own BVH only where order cannot matter
             assert i.traversal_used == (product_lib.RT_TRAVERSAL_REFERENCE if i.has_wrappers else product_lib.RT_TRAVERSAL_FAST)
-            assert i.kernel_mode == (1 if not i.has_wrappers else (2 if i.treelets + i.fused_instances else 3))
+            assert i.kernel_mode == ((5 if tiny else 1) if not i.has_wrappers else (2 if i.treelets + i.fused_instances else 3))
     hs.close()
 
 
@@ -64,6 +65,17 @@ def test_linear_program_of_the_cornell_box(product_lib):
     big = product_lib.HostScene(3).pack_info()                  # 7593 objects: far beyond the program limit, and it has treelets
     assert big.kernel_mode == 2 and big.program_ops == 0
     hs.close()
+
+
+def test_tiny_scenes_skip_their_bvh(product_lib):
+    """At most 4 spheres and 4 quads / triangles and no wrappers: every primitive is tested, two spheres at a time
+    (kernel mode 5).  The Perlin scenes 17 and 19 are such scenes; scene 18 (5 quads) and scene 2 (485 spheres) are not."""
+    modes = {}
+    for sid in (13, 15, 16, 17, 19, 18, 2):
+        hs = product_lib.HostScene(sid)
+        modes[sid] = hs.pack_info().kernel_mode
+        hs.close()
+    assert modes == {13: 5, 15: 5, 16: 5, 17: 5, 19: 5, 18: 1, 2: 1}
 
 
 def test_pack_info_rejects_bad_input(product_lib):
