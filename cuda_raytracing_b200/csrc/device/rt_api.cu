@@ -198,8 +198,9 @@ int rt_scene_upload(rt_context *ctx, const rt_scene_desc *desc, uint32_t travers
   return RT_OK;
 }
 
-// kernel variant: 1 = own BVH over the whole scene, 5 = tiny scene without wrappers (every primitive, no BVH), 3 = reference order as a linear program (small scenes with wrappers),
-// 2 = reference order with treelets / fused instances, 0 = reference order through the stack
+// kernel variant: 1 = own BVH over the whole scene, 5 = tiny scene without wrappers (every primitive, no BVH),
+// 3 = reference order as a linear program (small scenes with wrappers), 2 = reference order with treelets / fused
+// instances, 0 = reference order through the stack
 static int kernel_mode(const rtp::PackedScene &p) {
   if (p.traversal_used == RT_TRAVERSAL_FAST) return p.flat ? 5 : 1;
   if (p.treelets + p.fused_instances > 0) return 2;
@@ -353,8 +354,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
     // Multiplier: golden-ratio stride, coprime to the slot count, so slot -> slot * mul mod n is a permutation and
     // neighbours in the queue are far apart in the image.
     const bool tiny_image = a.claim_group == 1 && (double)count <= 2.0 * lanes;
-    const bool short_hybrid = mode == 2 &&
-                              count <= (1u << 20) && (double)spp * (double)count <= 1024.0 * lanes;
+    const bool short_hybrid = mode == 2 && count <= (1u << 20) && (double)spp * (double)count <= 1024.0 * lanes;
     const bool want_scatter = ctx->scatter >= 0 ? ctx->scatter == 1 : (tiny_image || short_hybrid);
     if (want_scatter && a.slots_per_chunk >= 64) {
       a.scatter_mul = scatter_multiplier(a.slots_per_chunk);
