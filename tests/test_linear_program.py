@@ -126,3 +126,26 @@ def test_program_export_rejects_bad_input(product_lib):
     import ctypes as C
     n = C.c_uint32(0)
     assert product_lib.lib().rt_scene_program(None, None, 0, C.byref(n)) != 0
+
+
+def test_wrapper_inside_a_wrapper_of_its_own_kind_keeps_the_stack_walk(product_lib):
+    """The reference's in_translation / in_rotation are flags, not counters: a translation met inside a translation is
+    taken for the way OUT.  Only the stack walk mirrors that, so such a scene gets no program (the shipped scenes never
+    nest like this; the array is patched by hand: scene 0's translate(rotate(pyramid)) becomes translate(translate()))."""
+    import ctypes as C
+    hs = product_lib.HostScene(0)
+    h, refs, arena = hs.arrays()
+    types = h[:, :4].copy().view(np.uint32)[:, 0]
+    rot = [i for i in range(len(h)) if types[i] == YROTATION]
+    assert len(rot) == 1
+    h[rot[0], :4] = np.frombuffer(struct.pack("<I", TRANSLATION), dtype=np.uint8)      # same layout: child u16 at +8, 12 bytes of record at +12
+    refs = np.ascontiguousarray(refs)
+    arena = np.ascontiguousarray(arena)
+    from cuda_raytracing_b200 import api
+    d = api.SceneDesc(h.ctypes.data, len(h), refs.ctypes.data, len(refs), hs.world.root_wref, arena.ctypes.data, len(arena))
+    info = api.PackInfo()
+    assert product_lib.lib().rt_scene_pack_info(C.byref(d), product_lib.RT_TRAVERSAL_AUTO, 8, 8, C.byref(info)) == 0
+    assert (info.kernel_mode, info.program_ops, info.has_wrappers) == (0, 0, 1)
+    n = C.c_uint32(7)
+    assert product_lib.lib().rt_scene_program(C.byref(d), None, 0, C.byref(n)) == 0 and n.value == 0
+    hs.close()
