@@ -13,14 +13,16 @@ from collections import defaultdict
 
 
 INCLUSIVE = False
+FRAME = None        # --frame FILE: attribute an instruction to its outermost inlining frame inside FILE (implies -gi)
 
 
 def line_map(obj, kernel):
     with tempfile.TemporaryDirectory() as d:
         subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(obj)], cwd=d, check=True, capture_output=True)
         cubin = [f for f in os.listdir(d) if f.endswith(".cubin")][0]
-        txt = subprocess.run(["nvdisasm", "-gi" if INCLUSIVE else "-g", "-c", os.path.join(d, cubin)], capture_output=True, text=True).stdout
+        txt = subprocess.run(["nvdisasm", "-gi" if (INCLUSIVE or FRAME) else "-g", "-c", os.path.join(d, cubin)], capture_output=True, text=True).stdout
     out, cur, on, fresh = {}, ("?", 0), False, True
+    chain, after_instr = [], True
     for ln in txt.splitlines():
         if ln.startswith(".text."):
             on = kernel in ln
@@ -31,11 +33,18 @@ def line_map(obj, kernel):
         if m:
             # with -gi a chain of "inner inlined at outer" lines precedes the instruction: the LAST line is the
             # outermost frame (the line of the kernel body that is responsible for the instruction)
-            cur = (os.path.basename(m.group(1)), int(m.group(2)))
+            if after_instr:
+                chain, after_instr = [], False
+            chain.append((os.path.basename(m.group(1)), int(m.group(2))))
+            cur = chain[-1]
+            if FRAME:
+                inside = [c for c in chain if c[0] == FRAME]
+                cur = inside[-1] if inside else chain[-1]
             continue
         m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(.*?);", ln)
         if m:
             out[int(m.group(1), 16)] = (cur, m.group(2).strip())
+            after_instr = True
     return out
 
 
@@ -44,6 +53,11 @@ def main():
     if "--inclusive" in sys.argv:          # attribute inlined code to the outermost call site
         INCLUSIVE = True
         sys.argv.remove("--inclusive")
+    global FRAME
+    if "--frame" in sys.argv:              # e.g. --frame rt_trace.cuh: per line of the walk instead of per line of the kernel body
+        i = sys.argv.index("--frame")
+        FRAME = sys.argv[i + 1]
+        del sys.argv[i:i + 2]
     rep, obj, kernel = sys.argv[1:4]
     top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
     lm = line_map(obj, kernel)
