@@ -18,7 +18,7 @@
 
 namespace {
 
-std::string g_last_error;
+thread_local std::string g_last_error;     // per host thread: contexts used from different threads do not share it
 
 struct DeviceBuffer {
   void *ptr = nullptr; size_t bytes = 0;
@@ -165,6 +165,7 @@ int rt_scene_upload(rt_context *ctx, const rt_scene_desc *desc, uint32_t travers
   if (!ctx || !desc) return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: NULL argument");
   RT_CUDA(ctx, cudaSetDevice(ctx->device));
   ctx->has_scene = false;
+  ctx->live_valid = false;                                 // parked XORWOW states belong to the scene they were rendered with
   ctx->packed = rtp::PackedScene();
   rtp::PackedScene &p = ctx->packed;
   int rc = rtp::pack_scene(*desc, traversal, p, ctx->treelet_min, ctx->fuse_min, ctx->linear == 0 ? 0u : rtp::PROGRAM_MAX_DEFAULT);
@@ -212,8 +213,9 @@ static int check_params(rt_context *ctx, const rt_render_params *p, int *row0, i
   if (!ctx->has_scene) return fail(ctx, RT_ERR_NO_SCENE, "rt_render: no scene uploaded");
   if (p->img_width <= 0 || p->img_height <= 0) return fail(ctx, RT_ERR_INVALID, "rt_render: image size must be positive");
   if ((int64_t)p->img_width * p->img_height > 0x7fffffffLL / 3) return fail(ctx, RT_ERR_UNSUPPORTED, "rt_render: image too large");
-  if (p->max_bounces < 0 || p->max_bounces > 255)
-    return fail(ctx, RT_ERR_UNSUPPORTED, "rt_render: max_bounces must be 0..255 (the reference's bounce stack counter is a u8)");
+  // max_bounces > 255 wraps modulo 256 exactly as in the reference, whose bounce-stack counter is a u8 (rt.cu:220, 1596:
+  // `b300` renders 44 bounces); the kernels apply `& 255`
+  if (p->max_bounces < 0) return fail(ctx, RT_ERR_INVALID, "rt_render: max_bounces must not be negative");
   int r0 = p->row_begin, r1 = p->row_end;
   if (r0 == 0 && r1 == 0) r1 = p->img_height;
   if (r0 < 0 || r1 > p->img_height || r0 >= r1) return fail(ctx, RT_ERR_INVALID, "rt_render: bad row range");
@@ -248,7 +250,11 @@ static int render_set(rt_context *ctx, const rt_render_params *p, int row0, int 
   out->first_pixel = out->banded ? 0 : (uint64_t)row0 * p->img_width;
   out->count = (uint64_t)out->rows * p->img_width;
   out->first_sub = out->first_pixel + p->subsequence_offset;
-  out->band_key = out->banded ? ((uint64_t)p->band_rows << 40) ^ ((uint64_t)p->band_period << 20) ^ p->band_phase ^ (1ull << 63) : 0;
+  // the subsequence runs of a banded set start at lo * img_width, so the key of the cached / live states carries the image
+  // size as well as the band parameters
+  out->band_key = out->banded ? (((uint64_t)p->band_rows << 40) ^ ((uint64_t)p->band_period << 20) ^ p->band_phase ^ (1ull << 63)) +
+                                    0x9e3779b97f4a7c15ull * (((uint64_t)(uint32_t)p->img_width << 32) | (uint32_t)p->img_height)
+                              : 0;
   return RT_OK;
 }
 
@@ -314,8 +320,9 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   a.rng_states = (uint32_t *)ctx->b_rng_states.ptr;
   a.progress = (uint32_t *)ctx->b_progress.ptr;
   int mode = kernel_mode(ctx->packed);
+  const int bounces = p->max_bounces & 255;                // u8 counter of the reference (rt.cu:220)
   // short-lived pixels (the regime that gets no time slices either) on the stackless walk: the 5 x 96-register build
-  if (mode == 3 && p->max_bounces <= 64 && (long long)p->samples_per_pixel * (long long)(p->max_bounces > 0 ? p->max_bounces : 1) <= 256) mode = 4;
+  if (mode == 3 && bounces <= 64 && (long long)p->samples_per_pixel * (long long)(bounces > 0 ? bounces : 1) <= 256) mode = 4;
   const double lanes = (double)ctx->sm_count * (mode == 3 ? 1024.0 : ((mode == 1 || mode == 5) ? 768.0 : 640.0));   // resident threads: 8, 6 or 5 blocks of 128 per SM
   {   // chunk size: about 1/32 of the samples one resident lane will produce, so that the tail of the render (lanes
       // idle because every remaining pixel is owned) is a few per cent; never below 8 samples per claim
@@ -327,7 +334,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
       if (chunk < 8) chunk = 8;
       // a pixel whose whole life is at most a few hundred bounces has no tail worth slicing: parking its state costs
       // more (C1, s16 b8: 1.31 -> 1.18 ms without slices; scene 3 at s16 b50 needs them: 143 vs 184 ms)
-      if ((long long)spp * (long long)(p->max_bounces > 0 ? p->max_bounces : 1) <= 256) chunk = spp;
+      if ((long long)spp * (long long)(bounces > 0 ? bounces : 1) <= 256) chunk = spp;
     }
     if (chunk > spp) chunk = spp;
     a.chunk_samples = chunk;
@@ -368,7 +375,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   a.counters = (unsigned long long *)ctx->b_counters.ptr;
   a.stack_entries = (int32_t)ctx->scene.stack_entries;
   a.img_width = p->img_width; a.img_height = p->img_height;
-  a.samples_per_pixel = p->samples_per_pixel; a.max_bounces = p->max_bounces;
+  a.samples_per_pixel = p->samples_per_pixel; a.max_bounces = bounces;
   a.first_pixel = (int32_t)first_pixel; a.pixel_count = (int32_t)count;
   a.defocus_angle = p->defocus_angle;
   memcpy(a.background, p->background, 12); memcpy(a.dv, p->pixel_delta_v, 12); memcpy(a.du, p->pixel_delta_u, 12);
@@ -442,6 +449,10 @@ int rt_render(rt_context *ctx, const rt_render_params *p, float *h_pixels, uint8
   int row0, row1;
   int rc = check_params(ctx, p, &row0, &row1);
   if (rc != RT_OK) return rc;
+  // the sums of a progressive render live in the CALLER's device buffer; this entry point renders into a scratch buffer
+  // that it may clear, so it cannot carry them on
+  if (p->flags & RT_RENDER_RESUME)
+    return fail(ctx, RT_ERR_INVALID, "rt_render: RT_RENDER_RESUME needs rt_render_device (the running sums stay in the caller's device buffer)");
   const double t0 = now_ms();
   RT_CUDA(ctx, cudaSetDevice(ctx->device));
   const uint64_t n = (uint64_t)p->img_width * p->img_height;

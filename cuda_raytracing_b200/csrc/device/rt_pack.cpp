@@ -170,6 +170,7 @@ struct Packer {
   bool fuse_instances;
   uint32_t fuse_min;                            // fewer qualifying chains than this (and no treelet): keep the plain walk
   uint32_t program_max;                         // longest reference-order walk (ops) laid out as a linear program; 0 = never
+  mutable bool too_deep = false;                // a recursion below hit its nesting guard: the scene is refused, never truncated
   Packer(const rt_scene_desc &desc, PackedScene &o, uint32_t tmin, uint32_t fmin, uint32_t pmax)
       : d(desc), out(o), treelet_min(tmin), fuse_instances(fmin > 0), fuse_min(fmin), program_max(pmax) {}
 
@@ -198,7 +199,8 @@ struct Packer {
   // exact stack need of the reference-order traversal (see trace_reference: every item is pushed, then popped and
   // worked on): `base` = entries below this subtree's root
   uint32_t stack_need(uint32_t href, uint32_t base, int guard) const {
-    if (guard > 64 || href >= d.hittable_count) return base;
+    if (guard > 64) { too_deep = true; return base; }
+    if (href >= d.hittable_count) return base;
     if (fused[href]) return base + fused[href] - 1;                        // nothing pushed, or the way out + a structure's children
     if (treelet_depth[href] > 0) return base + treelet_depth[href] + 1;    // one pending far child per level + the pair pushed last
     const rt_hittable &h = H(href);
@@ -249,7 +251,7 @@ struct Packer {
     return n;
   }
   void gather(uint32_t href, std::vector<Leaf> &lv, int guard) {
-    if (guard > 64) return;
+    if (guard > 64) { too_deep = true; return; }
     const rt_hittable &h = H(href);
     switch (h.type) {
       case RT_OBJ_SPHERE: { Leaf lf; lf.ref = tag[href]; lf.box = box_of(h.u.sphere.bbox); center_leaf(lf); lv.push_back(lf); } break;
@@ -264,7 +266,8 @@ struct Packer {
   }
   // top-down over the reference graph: the first BVH node on each path that is wrapper-free and big enough becomes a treelet
   void plant_treelets(uint32_t href, uint32_t min_prims, int guard) {
-    if (guard > 64 || href >= d.hittable_count) return;
+    if (guard > 64) { too_deep = true; return; }
+    if (href >= d.hittable_count) return;
     const rt_hittable &h = H(href);
     if (h.type == RT_OBJ_BVH_NODE) {
       if (treelet_depth[href] > 0) return;
@@ -406,7 +409,8 @@ struct Packer {
 
   // world-space copy of everything below `href` (FAST traversal)
   void flatten(uint32_t href, const Xf &xf, int guard) {
-    if (guard > 64 || href >= d.hittable_count) return;
+    if (guard > 64) { too_deep = true; return; }
+    if (href >= d.hittable_count) return;
     const rt_hittable &h = H(href);
     switch (h.type) {
       case RT_OBJ_SPHERE: {
@@ -553,6 +557,7 @@ struct Packer {
         const uint32_t href = d.world_refs[w];
         if (H(href).type != RT_OBJ_BVH_NODE) flatten(href, id, 0);
       }
+      if (too_deep) { out.error = "rt_scene_upload: objects nested deeper than 64 levels"; return RT_ERR_UNSUPPORTED; }
       if (leaves.empty()) { out.error = "rt_scene_upload: no primitives"; return RT_ERR_INVALID; }
       if (leaves.size() == 1) {                       // a root node with one real child and one empty box
         out.fast_nodes.resize(4);
@@ -572,8 +577,11 @@ struct Packer {
       out.has_fast = true;
     }
     out.traversal_used = want_fast ? RT_TRAVERSAL_FAST : RT_TRAVERSAL_REFERENCE;
-    // tiny scenes without wrappers (so the primitive arrays are exactly the scene): no BVH at all
-    if (want_fast && !out.has_wrappers && out.spheres.size() / 2 <= 4 && out.planars.size() / 4 <= 4) {
+    if (too_deep) { out.error = "rt_scene_upload: objects nested deeper than 64 levels"; return RT_ERR_UNSUPPORTED; }
+    // tiny scenes without wrappers whose every primitive record is reachable from the world list (so the primitive arrays
+    // are exactly the scene; an orphan hittable would be tested here and by no other walk): no BVH at all
+    if (want_fast && !out.has_wrappers && out.spheres.size() / 2 <= 4 && out.planars.size() / 4 <= 4 &&
+        leaves.size() == out.spheres.size() / 2 + out.planars.size() / 4) {
       out.flat = true;
       uint32_t k = 0;
       for (uint64_t i = 0; i < n; ++i) {

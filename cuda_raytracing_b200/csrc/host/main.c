@@ -43,6 +43,7 @@ int main(int argc, char *argv[]) {
   size_t n = (size_t)cam.img_width * cam.img_height;
   uint8_t *rgb8 = (uint8_t *)malloc(n * 3);
   rt_stats st;
+  memset(&st, 0, sizeof(st));
   rc = rt_render_world(ctx, &world, &settings, traversal, NULL, rgb8, &st);
   /* the reference prints these four lines whatever happened (rt.cu:1758-1768) */
   printf("cuda_calc launch error: %s\n", rc == RT_OK ? "no error" : rt_last_error_string(ctx));

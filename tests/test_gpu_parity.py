@@ -140,12 +140,28 @@ def test_texture_probe_vs_oracle(gpu_ctx, oracle, product_lib):
         L.orc_set_fma_profile(0)
 
 
-def _ref_gpu_image(scene, width, spp, bounces, height):
+def _require_reference_binary():
+    """The reference's own GPU binary is the tier-1 pin (the oracle differs from it wherever CUDA's libm differs from
+    glibc's): it travels to the box as a built file under oracle/_ref/.  Its absence FAILS the test -- a pin that
+    quietly drops out would leave noise / dielectric scenes held to a 97 % bar only."""
+    if not os.path.exists(REF_EXT):
+        pytest.fail("oracle/_ref/raytracing_ref_ext is missing: run `bash oracle/build_ref.sh` where /root/reference exists "
+                    "(the built binary travels with the snapshot)")
+
+
+def _ref_gpu_image(scene, width, spp, bounces, height, want_ms=False):
+    _require_reference_binary()
     with tempfile.TemporaryDirectory() as d:
         dump = os.path.join(d, "img.f32")
         env = dict(os.environ, RT_WIDTH=str(width), RT_DUMP_F32=dump, RT_NO_PPM="1")
-        subprocess.run([REF_EXT, str(scene), "s%d" % spp, "b%d" % bounces], cwd=d, env=env, capture_output=True, timeout=900, check=True)
-        return np.fromfile(dump, dtype=np.float32).reshape(height, width, 3)
+        if not width:
+            env.pop("RT_WIDTH")
+        out = subprocess.run([REF_EXT, str(scene), "s%d" % spp, "b%d" % bounces], cwd=d, env=env, capture_output=True, text=True, timeout=900, check=True)
+        img = np.fromfile(dump, dtype=np.float32).reshape(height, -1, 3)
+        if want_ms:
+            ms = [float(ln.split()[2][:-2]) for ln in out.stdout.splitlines() if ln.startswith("Rendering time:") and ln.endswith("ms")]
+            return img, (ms[0] if ms else None)
+        return img
 
 
 @pytest.mark.parametrize("sid", list(range(20)))
@@ -157,7 +173,7 @@ def test_image_vs_oracle_and_reference_gpu(gpu_ctx, oracle, product_lib, sid):
     cam = common.oracle_camera(oracle, p)
     want, want_rays = oracle.render(sc, cam, gpu_profile=True)
     n = p.img_width * p.img_height
-    ref = _ref_gpu_image(sid, width, spp, b, p.img_height) if os.path.exists(REF_EXT) else None
+    ref = _ref_gpu_image(sid, width, spp, b, p.img_height)       # mandatory: fails when the binary did not travel
     for trav in (product_lib.RT_TRAVERSAL_AUTO, product_lib.RT_TRAVERSAL_REFERENCE):
         gpu_ctx.upload(hs, trav)
         img, rgb8, st = gpu_ctx.render(p)
@@ -168,11 +184,11 @@ def test_image_vs_oracle_and_reference_gpu(gpu_ctx, oracle, product_lib, sid):
             assert st.rays == want_rays
             assert np.array_equal(common.bits(img), common.bits(want)), (sid, trav)
         assert np.array_equal(rgb8, oracle.resolve_rgb8(img))          # device resolve == the reference's gamma/quantise rule
-        if ref is not None:                                              # tier 1 against the reference's own GPU render
-            same = (common.bits(img) == common.bits(ref)).all(axis=2).mean()
-            within = (np.abs(rgb8.astype(np.int32) - oracle.resolve_rgb8(ref).astype(np.int32)).max(axis=2) <= 1).mean()
-            assert within >= 0.999, (sid, trav, within)
-            assert same >= 0.999, (sid, trav, same)
+        # tier 1 against the reference's own GPU render
+        same = (common.bits(img) == common.bits(ref)).all(axis=2).mean()
+        within = (np.abs(rgb8.astype(np.int32) - oracle.resolve_rgb8(ref).astype(np.int32)).max(axis=2) <= 1).mean()
+        assert within >= 0.999, (sid, trav, within)
+        assert same >= 0.999, (sid, trav, same)
     if sid in WRAPPER_SCENES:                                            # flattened instances: tier 2 only
         gpu_ctx.upload(hs, product_lib.RT_TRAVERSAL_AUTO)
         exact, e8, _ = gpu_ctx.render(hs.params(width, 64, b))
@@ -185,6 +201,38 @@ def test_image_vs_oracle_and_reference_gpu(gpu_ctx, oracle, product_lib, sid):
         fb = f8[:hb, :wb].reshape(hb // 8, 8, wb // 8, 8, 3).mean(axis=(1, 3))
         assert common.psnr8(eb, fb) >= 32.0, (sid, common.psnr8(eb, fb))
         assert abs(float(exact.mean()) - float(fast.mean())) <= 0.01 * max(float(exact.mean()), 1e-3) + 1e-3
+    hs.close()
+
+
+BASELINE_CONFIGS = {   # BASELINE.json configs at their full sizes: name -> (scene, spp, bounces, width override, pixels)
+    "C1": (0, 16, 8, 0, 800 * 450), "C2": (2, 256, 50, 0, 1200 * 675), "C3": (17, 512, 50, 0, 400 * 400),
+    "C3b": (19, 512, 50, 0, 1080 * 607), "C4": (1, 1024, 50, 0, 600 * 600), "C5r": (3, 16, 50, 0, 800 * 800),
+}
+
+
+@pytest.mark.parametrize("name", list(BASELINE_CONFIGS))
+def test_baseline_configs_vs_reference_gpu(gpu_ctx, oracle, product_lib, name):
+    """Tier 1 at the FULL size of every BASELINE.json config (C5 at its built-in 800x800 and 1/256 of its samples: the
+    reference needs 17.7 GB of colour stacks and hours at 4K s4096): the reference's own CUDA binary, run here on the
+    same GPU with its seed 1234, against RT_TRAVERSAL_AUTO.  Bar (north_star): |delta| <= 1/255 on >= 99.9 % of the 8-bit
+    pixels; in practice >= 99.9 % of the f32 pixels are bit-identical, which is asserted too."""
+    sid, spp, b, width, pixels = BASELINE_CONFIGS[name]
+    hs = product_lib.HostScene(sid)
+    p = hs.params(width, spp, b)
+    assert p.img_width * p.img_height == pixels
+    ref, ref_ms = _ref_gpu_image(sid, width, spp, b, p.img_height, want_ms=True)
+    assert ref.shape == (p.img_height, p.img_width, 3)
+    gpu_ctx.upload(hs, product_lib.RT_TRAVERSAL_AUTO)
+    img, rgb8, st = gpu_ctx.render(p)
+    same = int((common.bits(img) == common.bits(ref)).all(axis=2).sum())
+    d8 = np.abs(rgb8.astype(np.int32) - oracle.resolve_rgb8(ref).astype(np.int32)).max(axis=2)
+    print("baseline %s: scene %d %dx%d s%d b%d: %d / %d f32 pixels bit-identical, %d 8-bit pixels differ by more than 1; ours %.2f ms "
+          "(kernel mode %d), reference %.2f ms" % (name, sid, p.img_width, p.img_height, spp, b, same, pixels, int((d8 > 1).sum()),
+                                                  st.render_ms, hs.pack_info().kernel_mode, ref_ms or -1))
+    assert st.paths == pixels * spp
+    assert same >= 0.999 * pixels, (name, same, pixels)
+    assert (d8 <= 1).mean() >= 0.999, name
+    assert np.array_equal(rgb8, oracle.resolve_rgb8(img))
     hs.close()
 
 
@@ -233,9 +281,14 @@ def test_edge_cases(gpu_ctx, product_lib):
     assert img.shape[:2] == (1, 2) and np.isfinite(img).all()
     with pytest.raises(product_lib.RtError):    # W=1 gives H=0: rejected, not rendered
         gpu_ctx.render(hs.params(1, 3, 5))
-    p = hs.params(40, 2, 300)                   # b > 255 is rejected (the reference's u8 counter would wrap)
-    with pytest.raises(product_lib.RtError):
-        gpu_ctx.render(p)
+    a, _, _ = gpu_ctx.render(hs.params(40, 2, 300))    # b > 255 wraps like the reference's u8 counter: b300 is b44
+    w, _, _ = gpu_ctx.render(hs.params(40, 2, 44))
+    assert np.array_equal(common.bits(a), common.bits(w))
+    z, _, st = gpu_ctx.render(hs.params(40, 2, 256))   # ... and b256 is b0: black
+    assert not z.any() and st.rays == 0
+    q = hs.params(40, 2, 4, flags=product_lib.RT_RENDER_OUTPUT_SUM | product_lib.RT_RENDER_RESUME)
+    with pytest.raises(product_lib.RtError):    # the host-buffer entry point cannot carry sums on: refused, not wrong
+        gpu_ctx.render(q)
     with pytest.raises(product_lib.RtError):
         product_lib.Context(0).render(hs.params(8, 1, 1))    # no scene uploaded
     hs.close()
@@ -251,30 +304,42 @@ def test_cli_writes_reference_ppm(product_lib, oracle):
         assert lines[2].startswith("Rendering time: ") and lines[2].endswith("ms") and lines[3].endswith("s")
         data = open(os.path.join(d, "mblur.ppm"), "rb").read()
         assert data.startswith(b"P6\n800 450\n255\n") and len(data) == len(b"P6\n800 450\n255\n") + 800 * 450 * 3
-        if os.path.exists(os.path.join(common.ROOT, "oracle", "_ref", "raytracing_ref")):
+        _require_reference_binary()
+        if True:
             d2 = os.path.join(d, "ref"); os.mkdir(d2)
             subprocess.run([os.path.join(common.ROOT, "oracle", "_ref", "raytracing_ref"), "13", "s2", "b4"], cwd=d2, capture_output=True, timeout=600, check=True)
             assert open(os.path.join(d2, "mblur.ppm"), "rb").read() == data      # byte-identical file
 
 
+TIER2_RECORD = os.path.join(common.ROOT, "gpurun_out", "tier2_psnr.jsonl")
+
+
 @pytest.mark.gpu
-@pytest.mark.parametrize("sid,floor_db", [(0, 40.0), (1, 30.0)])
-def test_tier2_converged_images_vs_reference_gpu(gpu_ctx, oracle, product_lib, sid, floor_db):
+@pytest.mark.parametrize("sid,width,abs_floor_db", [(0, 128, 40.0), (1, 128, None), (3, 200, None)])
+def test_tier2_converged_images_vs_reference_gpu(gpu_ctx, oracle, product_lib, sid, width, abs_floor_db):
     """Tier 2 (north_star): at 4096 spp the statistical modes -- flattened instances (RT_TRAVERSAL_FAST) and sample
     sharding (2 virtual ranks x 2048 spp, disjoint XORWOW subsequences, summed) -- match the reference's own GPU render.
-    PSNR on the 8-bit images, tolerance: >= 40 dB on the sky-lit scene; the Cornell box (small light, black background)
-    is noise-limited at 4096 spp, two independent estimates of it differ by more than that, so its floor is lower."""
-    if not os.path.exists(REF_EXT):
-        pytest.skip("reference binary not built")
+    PSNR on the 8-bit images.  What two 4096-spp estimates CAN agree to depends on the scene: the sky-lit scene 0 passes
+    north_star's 40 dB outright; the Cornell box and the final scene (scene 3, the one C5 renders in statistical mode at 4K)
+    are lit by one small quad on a black background and are noise-limited far below that at 4096 spp.  Their floor is
+    therefore MEASURED in the same test: an independent run of the EXACT estimator (RT_TRAVERSAL_AUTO, the reference's
+    arithmetic and visiting order, another XORWOW subsequence block) against the same reference image.  A statistical
+    mode passes when it is within 1 dB of that -- i.e. it is as close to the reference as the reference's own algorithm
+    is to itself with other random numbers.  The PSNRs are printed and written to gpurun_out/tier2_psnr.jsonl."""
+    import json
     hs = product_lib.HostScene(sid)
-    width, spp, b = 128, 4096, 50
+    spp, b = 4096, 50
     p = hs.params(width, spp, b)
+    n = p.img_width * p.img_height
     ref8 = oracle.resolve_rgb8(_ref_gpu_image(sid, width, spp, b, p.img_height))
+    gpu_ctx.upload(hs, product_lib.RT_TRAVERSAL_AUTO)
+    same8 = gpu_ctx.render(p)[1]                                         # tier 1 at 4096 spp, for the record
+    _, indep8, _ = gpu_ctx.render(hs.params(width, spp, b, subsequence_offset=7 * n))
+    db_floor = common.psnr8(indep8, ref8)
     gpu_ctx.upload(hs, product_lib.RT_TRAVERSAL_FAST)
     _, fast8, st = gpu_ctx.render(p)
     assert st.traversal_used == product_lib.RT_TRAVERSAL_FAST
     db_fast = common.psnr8(fast8, ref8)
-    n = p.img_width * p.img_height
     total = np.zeros((p.img_height, p.img_width, 3), np.float32)
     for g in range(2):                                                   # the reduce of bench.py / render.py, done on the host
         q = hs.params(width, spp // 2, b, subsequence_offset=g * n, flags=product_lib.RT_RENDER_OUTPUT_SUM)
@@ -282,8 +347,18 @@ def test_tier2_converged_images_vs_reference_gpu(gpu_ctx, oracle, product_lib, s
         total += part
     shard8 = oracle.resolve_rgb8(total * np.float32(1.0 / spp))
     db_shard = common.psnr8(shard8, ref8)
-    print("tier2 scene %d: PSNR fast %.2f dB, sample-sharded %.2f dB" % (sid, db_fast, db_shard))
-    assert db_fast >= floor_db and db_shard >= floor_db, (sid, db_fast, db_shard)
+    rec = {"scene": sid, "width": p.img_width, "height": p.img_height, "spp": spp, "bounces": b,
+           "psnr_exact_same_stream_db": common.psnr8(same8, ref8), "psnr_exact_independent_stream_db": db_floor,
+           "psnr_fast_db": db_fast, "psnr_sample_sharded_db": db_shard}
+    print("tier2 " + json.dumps(rec))
+    try:
+        os.makedirs(os.path.dirname(TIER2_RECORD), exist_ok=True)
+        with open(TIER2_RECORD, "a") as f:
+            f.write(json.dumps(rec) + "\n")
+    except OSError:
+        pass
+    floor = db_floor - 1.0 if abs_floor_db is None else abs_floor_db
+    assert db_fast >= floor and db_shard >= floor, rec
     hs.close()
 
 

@@ -83,3 +83,67 @@ def test_pack_info_rejects_bad_input(product_lib):
     with pytest.raises(product_lib.RtError):
         hs.pack_info(traversal=7)
     hs.close()
+
+
+def _desc_from_arrays(product_lib, h, r, t, root):
+    import ctypes as C
+    import numpy as np
+    h = np.ascontiguousarray(h, dtype=np.uint8); r = np.ascontiguousarray(r, dtype=np.uint16); t = np.ascontiguousarray(t, dtype=np.uint8)
+    d = product_lib.api.SceneDesc(h.ctypes.data, h.shape[0], r.ctypes.data, r.shape[0], root, t.ctypes.data, t.shape[0])
+    return d, (h, r, t)
+
+
+def _pack_info(product_lib, desc, traversal=0):
+    import ctypes as C
+    info = product_lib.api.PackInfo()
+    rc = product_lib.lib().rt_scene_pack_info(C.byref(desc), traversal, 8, 8, C.byref(info))
+    return rc, info
+
+
+def test_orphan_hittable_keeps_the_bvh(product_lib):
+    """The tiny-scene walk tests every primitive RECORD, so it is only chosen when every record is reachable from the
+    world list: a caller-supplied array with an orphan hittable goes through the BVH (which never sees the orphan),
+    like the reference."""
+    import numpy as np
+    hs = product_lib.HostScene(17)
+    h, r, t = hs.arrays()
+    desc, keep = _desc_from_arrays(product_lib, h, r, t, hs.world.root_wref)
+    rc, info = _pack_info(product_lib, desc)
+    assert rc == 0 and info.kernel_mode == 5 and info.spheres == 2
+    orphan = np.concatenate([h, h[:1]])                     # a copy of sphere 0 that no world ref names
+    desc, keep = _desc_from_arrays(product_lib, orphan, r, t, hs.world.root_wref)
+    rc, info = _pack_info(product_lib, desc)
+    assert rc == 0 and info.spheres == 3 and info.kernel_mode == 1
+    hs.close()
+
+
+def test_nesting_beyond_the_guard_is_refused(product_lib):
+    """70 translations around one sphere: deeper than the packer's recursion guard.  Refused with RT_ERR_UNSUPPORTED in
+    every mode instead of silently dropping the primitive."""
+    import numpy as np
+    hs = product_lib.HostScene(13)
+    h, r, t = hs.arrays()
+    sphere = h[0].copy()
+    assert int(sphere[:4].view(np.uint32)[0]) == 0            # RT_OBJ_SPHERE
+    depth = 70
+    arr = np.zeros((depth + 2, 120), np.uint8)
+    arr[0] = sphere
+    for k in range(1, depth + 1):                             # translation k wraps hittable k - 1
+        arr[k, :4] = np.array([4], np.uint32).view(np.uint8)
+        arr[k, 8:10] = np.array([k - 1], np.uint16).view(np.uint8)
+        arr[k, 12:24] = np.array([0.01, 0.0, 0.0], np.float32).view(np.uint8)
+    arr[depth + 1, :4] = np.array([1], np.uint32).view(np.uint8)          # BVH node over world ref 0 (left == right)
+    arr[depth + 1, 8:12] = np.array([0, 0], np.uint16).view(np.uint8)
+    arr[depth + 1, 12:36] = np.array([-1e3, 1e3, -1e3, 1e3, -1e3, 1e3], np.float32).view(np.uint8)
+    refs = np.array([depth, depth + 1], np.uint16)            # world: the outermost wrapper, then the node
+    for trav in (0, 1, 2):
+        desc, keep = _desc_from_arrays(product_lib, arr, refs, t, 1)
+        rc, info = _pack_info(product_lib, desc, trav)
+        assert rc == -4, (trav, rc)                           # RT_ERR_UNSUPPORTED
+    shallow = arr.copy()
+    shallow[depth + 1, 8:12] = np.array([0, 0], np.uint16).view(np.uint8)
+    refs2 = np.array([10, depth + 1], np.uint16)              # ten wrappers: fine
+    desc, keep = _desc_from_arrays(product_lib, shallow, refs2, t, 1)
+    rc, info = _pack_info(product_lib, desc, 0)
+    assert rc == 0 and info.has_wrappers == 1
+    hs.close()
