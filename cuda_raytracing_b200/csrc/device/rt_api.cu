@@ -385,6 +385,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   a.resume = resume ? 1u : 0u;
   a.count_rays = (p->flags & (RT_RENDER_COUNT_RAYS | RT_RENDER_COUNT_OPS)) ? 1u : 0u;
   a.count_ops = (p->flags & RT_RENDER_COUNT_OPS) ? 1u : 0u;
+  a.forward = (p->flags & RT_RENDER_FORWARD_THROUGHPUT) ? 1u : 0u;
   if (mode >= 3) a.stack_entries = 0;                      // neither the linear program nor the tiny-scene walk needs a traversal stack
   RT_CUDA(ctx, rtk::launch_render(a, mode, ctx->sm_count, s, &ctx->last_launch));
   ++launches;

@@ -121,6 +121,7 @@ struct RenderArgs {
   uint32_t resume;               // chunk 0 starts from the sums already in `pixels` (progressive accumulation)
   uint32_t count_rays;
   uint32_t count_ops;            // run the instrumented kernel variant (per-ray operation counts for F_ray)
+  uint32_t forward;              // RT_RENDER_FORWARD_THROUGHPUT: attenuation product carried forwards in registers
 };
 
 constexpr int STACK_CAPACITY = 32;     // traversal stack entries per thread (shared memory, [slot][thread])

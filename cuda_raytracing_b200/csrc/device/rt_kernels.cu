@@ -110,7 +110,14 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
   const V3 bg = v3(a.background[0], a.background[1], a.background[2]);
   const int capacity = a.max_bounces & 255;            // RayColorStack.max_count is a u8 (rt.cu:220, 1596)
 
-  float att_r[MAXB], att_g[MAXB], att_b[MAXB];         // thread-local attenuation stack (unwound backwards)
+  // MAXB > 0: thread-local attenuation stack, unwound backwards like the reference's (result = att * result + emission, the
+  // same roundings: bit-identical).  MAXB == 0 (RT_RENDER_FORWARD_THROUGHPUT): the product of the attenuations is carried
+  // forwards in three registers instead.  Emission only ever ENDS a path here (lights do not scatter, rt.cu:452-490), so
+  // the radiance is e * a_n * ... * a_1 either way; only the association of the product differs (~n * 2^-24 relative,
+  // output-only arithmetic: it cannot change a path).
+  constexpr bool FWD = MAXB == 0;
+  float att_r[FWD ? 1 : MAXB], att_g[FWD ? 1 : MAXB], att_b[FWD ? 1 : MAXB];
+  V3 thr = v3(1.0f, 1.0f, 1.0f);
 
   // Work item = (chunk of `chunk_samples` samples, pixel), handed out chunk-major: item = chunk * pixel_count + pixel.
   // A pixel's samples are produced strictly in order from its own XORWOW state (that is the reference's stream),
@@ -204,6 +211,7 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
       d = v3(ffma(yo, dv.x, d.x), ffma(yo, dv.y, d.y), ffma(yo, dv.z, d.z));
       ray.o = o; ray.d = d; ray.time = rng_uniform(rng);
       budget = capacity; depth = 0;
+      if (FWD) thr = v3(1.0f, 1.0f, 1.0f);
     }
 
     // ---- (2) one bounce: closest hit, (3) emission + scatter ----
@@ -228,7 +236,8 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
         if (rts::scatter(sc, m0, m1, ray.d, h, U, rtest, perlin, dout, att, &noise_pending)) {
           noise_p = h.p; noise_scale = m1.w;
           ray.o = h.p; ray.d = dout;
-          if (depth != capacity) { att_r[depth] = att.x; att_g[depth] = att.y; att_b[depth] = att.z; ++depth; }
+          if (FWD) { if (!noise_pending) thr = v3(fmul(thr.x, att.x), fmul(thr.y, att.y), fmul(thr.z, att.z)); }
+          else if (depth != capacity) { att_r[depth] = att.x; att_g[depth] = att.y; att_b[depth] = att.z; ++depth; }
           --budget;
           done = (budget <= 0);                          // bounce budget spent: result stays (0,0,0) (Q14)
         } else {
@@ -248,15 +257,17 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
         const float turb = rts::coop_turbulence7(perlin, coop, mn, noise_pending, noise_p);
         if (noise_pending) {                              // the slot scatter pushed (depth - 1) gets the colour
           const V3 c = rts::noise_colour(turb, noise_scale, noise_p.z);
-          att_r[depth - 1] = c.x; att_g[depth - 1] = c.y; att_b[depth - 1] = c.z;
+          if (FWD) thr = v3(fmul(thr.x, c.x), fmul(thr.y, c.y), fmul(thr.z, c.z));
+          else { att_r[depth - 1] = c.x; att_g[depth - 1] = c.y; att_b[depth - 1] = c.z; }
         }
       }
     }
 
     // ---- (5) unwind, accumulate, resolve ----
     if (done) {
+      if (FWD) result = v3(fmul(result.x, thr.x), fmul(result.y, thr.y), fmul(result.z, thr.z));
       if (result.x == 0.0f && result.y == 0.0f && result.z == 0.0f) depth = 0;   // 0 stays +0 through every fma(0, att, 0)
-      while (depth > 0) {                                // result = att (.) result + emission, one fma per channel
+      while (!FWD && depth > 0) {                                // result = att (.) result + emission, one fma per channel
         --depth;
         result = v3(ffma(result.x, att_r[depth], 0.0f), ffma(result.y, att_g[depth], 0.0f), ffma(result.z, att_b[depth], 0.0f));
       }
@@ -537,6 +548,14 @@ cudaError_t launch_render(const rtd::RenderArgs &args, int mode, int sm_count, c
     if (mode == 5) return launch_render_t<5, 256, true>(args, sm_count, stream, info);
     if (mode >= 3) return launch_render_t<3, 256, true>(args, sm_count, stream, info);
     return launch_render_t<1, 256, true>(args, sm_count, stream, info);
+  }
+  if (args.forward) {                                    // RT_RENDER_FORWARD_THROUGHPUT: no attenuation stack (MAXB = 0)
+    if (mode == 0) return launch_render_t<0, 0, false>(args, sm_count, stream, info);
+    if (mode == 2) return launch_render_t<2, 0, false>(args, sm_count, stream, info);
+    if (mode == 5) return launch_render_t<5, 0, false>(args, sm_count, stream, info);
+    if (mode == 4) return launch_render_t<4, 0, false>(args, sm_count, stream, info);
+    if (mode == 3) return launch_render_t<3, 0, false>(args, sm_count, stream, info);
+    return launch_render_t<1, 0, false>(args, sm_count, stream, info);
   }
   if (mode == 0) return small ? launch_render_t<0, 64, false>(args, sm_count, stream, info) : launch_render_t<0, 256, false>(args, sm_count, stream, info);
   if (mode == 2) return small ? launch_render_t<2, 64, false>(args, sm_count, stream, info) : launch_render_t<2, 256, false>(args, sm_count, stream, info);

@@ -37,7 +37,8 @@ int rt_render_world(rt_context *ctx, rt_world *world, const rt_render_settings *
   if (rc != RT_OK) return rc;
   rt_render_params p;
   rt_render_params_from_camera(settings, &cam, &p);
-  p.flags = RT_RENDER_COUNT_RAYS;
+  /* like render(), which runs init_gpu_data on every call (rt.cu:1739-1748): the XORWOW states are recomputed, not reused */
+  p.flags = RT_RENDER_COUNT_RAYS | RT_RENDER_NO_RNG_CACHE;
   return rt_render(ctx, &p, h_pixels_rgb, h_rgb8, stats);
 }
 

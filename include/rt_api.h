@@ -77,6 +77,11 @@ enum {
   RT_RENDER_NO_RNG_CACHE = 2u,    /* recompute the XORWOW states even if cached from the previous call */
   RT_RENDER_COUNT_RAYS = 4u,      /* fill rt_stats.rays (warp-aggregated counter; small cost) */
   RT_RENDER_COUNT_OPS = 8u,       /* instrumented kernel variant: fill rt_stats.ops (never use for timing) */
+  RT_RENDER_FORWARD_THROUGHPUT = 32u, /* NOT bit-identical: carry the product of a path's attenuations forwards in three
+                                     registers instead of unwinding the reference's attenuation stack backwards.  Emission
+                                     only ever ends a path in this renderer, so the value is the same product associated the
+                                     other way round (<= ~n * 2^-24 relative per sample); it is output-only arithmetic and
+                                     cannot change a path.  Inside tier 1's 1/255 tolerance, outside bit-identity. */
   RT_RENDER_RESUME = 16u          /* progressive accumulation: carry on from the state the previous
                                      render of the same seed / rows / subsequence offset left behind -- the per-pixel XORWOW
                                      states where it stopped, and the per-pixel SUMS still in d_pixels_rgb (needs

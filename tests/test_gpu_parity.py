@@ -560,3 +560,22 @@ def test_image_texture_from_decoded_pixels(gpu_ctx, oracle, product_lib):
     finally:
         L.orc_set_fma_profile(0)
     hs.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sid", [2, 1, 17, 3])
+def test_forward_throughput_mode_is_within_tolerance(gpu_ctx, oracle, product_lib, sid):
+    """RT_RENDER_FORWARD_THROUGHPUT carries the product of a path's attenuations forwards in registers instead of unwinding
+    the reference's stack backwards: the same paths (same rays, same RNG draws), the same factors, another association of
+    the product.  Stated tolerance: relative 1e-5 per pixel on the f32 image (n * 2^-24 per sample with n <= 50 bounces),
+    8-bit image within 1 everywhere -- far inside tier 1's 1/255, but not bit-identical, hence a flag and not the default."""
+    hs = product_lib.HostScene(sid)
+    gpu_ctx.upload(hs, product_lib.RT_TRAVERSAL_AUTO)
+    p = hs.params(160 if sid != 3 else 96, 16, 50)
+    exact, e8, st0 = gpu_ctx.render(p)
+    q = hs.params(160 if sid != 3 else 96, 16, 50, flags=product_lib.RT_RENDER_COUNT_RAYS | product_lib.RT_RENDER_FORWARD_THROUGHPUT)
+    fwd, f8, st1 = gpu_ctx.render(q)
+    assert st0.rays == st1.rays                                        # the paths are the same paths
+    assert np.all(np.abs(fwd - exact) <= 1e-5 * np.abs(exact) + 1e-9), float(np.abs(fwd - exact).max())
+    assert np.abs(f8.astype(np.int32) - e8.astype(np.int32)).max() <= 1
+    hs.close()
