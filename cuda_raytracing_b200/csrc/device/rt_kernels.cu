@@ -33,6 +33,9 @@ using rts::PerlinSmem;
 using rtt::Hit;
 using rtt::Ray;
 
+#ifndef RT_NOISE_AT_PATH_END
+#define RT_NOISE_AT_PATH_END 1
+#endif
 constexpr int RT_BLOCK = 128;
 // resident blocks per SM asked of the compiler: 6 x 128 threads x 80 registers for the own-BVH walk, 5 x 96 for the
 // reference-order walk (measured both ways, profiles/r1_sweep_tile_occ.jsonl; tools/build_variants.sh overrides)
@@ -98,7 +101,7 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
   float *coop = nullptr;                                // per-warp scratch of the cooperative turbulence
   if (sc.perlin_tables > 0) {
     perlin = reinterpret_cast<PerlinSmem *>(smem + a.stack_entries * RT_BLOCK);
-    coop = reinterpret_cast<float *>(perlin + 1) + (threadIdx.x >> 5) * rts::COOP_WORDS_PER_WARP;
+    coop = reinterpret_cast<float *>(perlin + 1) + (threadIdx.x >> 5) * rts::SCRATCH_WORDS_PER_WARP;
     stage_perlin(sc, perlin);
     __syncthreads();
   }
@@ -118,6 +121,11 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
   constexpr bool FWD = MAXB == 0;
   float att_r[FWD ? 1 : MAXB], att_g[FWD ? 1 : MAXB], att_b[FWD ? 1 : MAXB];
   V3 thr = v3(1.0f, 1.0f, 1.0f);
+  // noise-textured bounces park {point, scale} in their slot; evaluated when (and if) the path has something to unwind
+  constexpr bool DEFER = !FWD && (RT_NOISE_AT_PATH_END != 0);
+  float att_s[DEFER ? MAXB : 1];
+  uint8_t nslot[DEFER ? MAXB : 1];                       // the parked slots of the current path, in order
+  int n_noise = 0;
 
   // Work item = (chunk of `chunk_samples` samples, pixel), handed out chunk-major: item = chunk * pixel_count + pixel.
   // A pixel's samples are produced strictly in order from its own XORWOW state (that is the reference's stream),
@@ -250,8 +258,13 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
       }
     }
 
-    // ---- (3b) Perlin textures of this bounce, all lanes of the warp working for the lanes that need one ----
-    if (perlin != nullptr) {                              // block-uniform
+    // ---- (3b) Perlin textures: parked until the path ends (DEFER), or evaluated now by the whole warp ----
+    if (DEFER) {
+      if (noise_pending) {
+        att_r[depth - 1] = noise_p.x; att_g[depth - 1] = noise_p.y; att_b[depth - 1] = noise_p.z; att_s[depth - 1] = noise_scale;
+        nslot[n_noise++] = (uint8_t)(depth - 1);
+      }
+    } else if (perlin != nullptr) {                       // block-uniform
       const unsigned mn = __ballot_sync(full, noise_pending);
       if (mn) {
         const float turb = rts::coop_turbulence7(perlin, coop, mn, noise_pending, noise_p);
@@ -264,6 +277,12 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
     }
 
     // ---- (5) unwind, accumulate, resolve ----
+    if (DEFER && perlin != nullptr) {                     // block-uniform
+      const bool unwinds = done && !(result.x == 0.0f && result.y == 0.0f && result.z == 0.0f);
+      if (__any_sync(full, unwinds && n_noise > 0))
+        rts::coop_resolve_noise(perlin, coop, unwinds ? n_noise : 0, nslot, att_r, att_g, att_b, att_s);
+      if (done) n_noise = 0;
+    }
     if (done) {
       if (FWD) result = v3(fmul(result.x, thr.x), fmul(result.y, thr.y), fmul(result.z, thr.z));
       if (result.x == 0.0f && result.y == 0.0f && result.z == 0.0f) depth = 0;   // 0 stays +0 through every fma(0, att, 0)
@@ -502,7 +521,7 @@ cudaError_t launch_probe_texture(const rtd::Scene &scene, uint64_t n, uint32_t t
 template <int MODE, int MAXB, bool COUNT>
 static cudaError_t launch_render_t(const RenderArgs &args, int sm_count, cudaStream_t stream, LaunchInfo *info) {
   size_t smem = sizeof(uint32_t) * (size_t)args.stack_entries * RT_BLOCK;
-  if (args.scene.perlin_tables > 0) smem += sizeof(PerlinSmem) + sizeof(float) * rts::COOP_WORDS_PER_WARP * (RT_BLOCK / 32);
+  if (args.scene.perlin_tables > 0) smem += sizeof(PerlinSmem) + sizeof(float) * rts::SCRATCH_WORDS_PER_WARP * (RT_BLOCK / 32);
   auto kernel = render_kernel<MODE, MAXB, COUNT>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;

@@ -84,6 +84,7 @@ __device__ __forceinline__ float perlin_turbulence7(const T &tab, V3 p) {
 // reference's accumulate chain over its 7 values: same bits, 32 lanes busy instead of the few that hit.
 // scratch: 3 * 32 floats of points + 7 * 32 floats of octave values per warp.
 constexpr int COOP_WORDS_PER_WARP = 3 * 32 + 7 * 32;
+constexpr int SCRATCH_WORDS_PER_WARP = 4 * 32 + 7 * 32 + 32;      // the larger of this and coop_resolve_noise's (below)
 __device__ __forceinline__ float coop_turbulence7(const PerlinSmem *table, float *scratch, unsigned requesters, bool mine, V3 p) {
   const unsigned lane = threadIdx.x & 31u;
   float *pts = scratch, *vals = scratch + 3 * 32;
@@ -105,6 +106,65 @@ __device__ __forceinline__ float coop_turbulence7(const PerlinSmem *table, float
   }
   __syncwarp();                                                               // scratch is reused by the next call
   return fabsf(accum);
+}
+
+// ---- the noise textures of finished paths, all at once ----------------------------------------------------------------
+// The attenuation of a bounce is not read before its path ends (the unwind), and not at all when the path ends with
+// radiance 0 (bounce budget spent, or a black background): so a noise-textured bounce only parks its point in its
+// attenuation slot, and the warp evaluates the parked points of the lanes whose path just ended with something to
+// unwind -- up to 32 points per round, 7 octaves each dealt round-robin to all 32 lanes, then one lane per point folds the
+// octaves in the reference's order and takes the sine.  Same perlin_noise / fold / noise_colour as the per-bounce
+// evaluation: same bits.  What it buys: the slowest pixels of the Perlin scenes (between the spheres almost every path
+// spends its 50 bounces and returns 0) never evaluate a texture at all, and a path that does is resolved with all lanes
+// busy instead of 7 per request.
+// scratch per warp: 32 x {x, y, z, scale} + 7 x 32 octave values + 32 colours
+
+__device__ __forceinline__ V3 noise_colour(float turb, float scale, float z);
+__device__ __forceinline__ void coop_resolve_noise(const PerlinSmem *table, float *scratch, int n_mine, const uint8_t *nslot,
+                                                   float *att_r, float *att_g, float *att_b, const float *att_s) {
+  const unsigned full = 0xffffffffu;
+  const int lane = (int)(threadIdx.x & 31u);
+  float *pts = scratch, *vals = scratch + 4 * 32, *cols = scratch + 4 * 32 + 7 * 32;
+  PerlinShared tab; tab.t = table;
+  int served = 0, remaining = n_mine;
+  for (;;) {
+    if (!__any_sync(full, remaining > 0)) break;
+    const int want = remaining < 32 ? remaining : 32;
+    int incl = want;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(full, incl, o); if (lane >= o) incl += v; }
+    const int excl = incl - want;
+    int total = __shfl_sync(full, incl, 31);
+    if (total > 32) total = 32;
+    int take = 32 - excl; take = take < 0 ? 0 : (take < want ? take : want);
+    for (int k = 0; k < take; ++k) {
+      const int j = nslot[served + k];
+      float *q = pts + 4 * (excl + k);
+      q[0] = att_r[j]; q[1] = att_g[j]; q[2] = att_b[j]; q[3] = att_s[j];
+    }
+    __syncwarp();
+    const int tasks = total * 7;
+    for (int t = lane; t < tasks; t += 32) {
+      const int req = t / 7, oct = t - req * 7;
+      const float s = (float)(1 << oct);                                      // p * 2^oct == oct doublings, exactly
+      vals[t] = perlin_noise(tab, v3(fmul(pts[4 * req], s), fmul(pts[4 * req + 1], s), fmul(pts[4 * req + 2], s)));
+    }
+    __syncwarp();
+    if (lane < total) {
+      float accum = 0.0f, weight = 1.0f;
+#pragma unroll
+      for (int o = 0; o < 7; ++o) { accum = ffma(weight, vals[7 * lane + o], accum); weight = fmul(weight, 0.5f); }
+      cols[lane] = noise_colour(fabsf(accum), pts[4 * lane + 3], pts[4 * lane + 2]).x;
+    }
+    __syncwarp();
+    for (int k = 0; k < take; ++k) {
+      const int j = nslot[served + k];
+      const float c = cols[excl + k];
+      att_r[j] = c; att_g[j] = c; att_b[j] = c;
+    }
+    served += take; remaining -= take;
+    __syncwarp();                                                             // scratch is reused by the next round
+  }
 }
 
 // noise texture colour (rt.cu:386-395): 0.5*(1 + sin(scale*z + 10*turb))
