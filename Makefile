@@ -22,15 +22,17 @@ $(BUILD)/rt_kernels.o: $(DEV)/rt_kernels.cu $(DEV)/*.cuh $(DEV)/*.h include/*.h 
 	$(NVCC) $(NVFLAGS) -c $< -o $@
 $(BUILD)/rt_api.o: $(DEV)/rt_api.cu $(DEV)/*.h include/*.h | $(BUILD)
 	$(NVCC) $(NVFLAGS) -c $< -o $@
+$(BUILD)/rt_group.o: $(DEV)/rt_group.cu $(DEV)/*.h include/*.h | $(BUILD)
+	$(NVCC) $(NVFLAGS) -c $< -o $@
 $(BUILD)/rt_pack.o: $(DEV)/rt_pack.cpp $(DEV)/*.h include/*.h | $(BUILD)
 	$(CXX) $(CXXFLAGS) -c $< -o $@
 $(BUILD)/%.o: $(HOST)/%.c include/*.h | $(BUILD)
 	$(CC) $(CFLAGS) -c $< -o $@
 
-OBJS := $(BUILD)/rt_kernels.o $(BUILD)/rt_api.o $(BUILD)/rt_pack.o $(BUILD)/rt_world.o $(BUILD)/rt_scenes.o $(BUILD)/rt_host.o
+OBJS := $(BUILD)/rt_kernels.o $(BUILD)/rt_api.o $(BUILD)/rt_group.o $(BUILD)/rt_pack.o $(BUILD)/rt_world.o $(BUILD)/rt_scenes.o $(BUILD)/rt_host.o
 
 $(LIB): $(OBJS)
-	$(NVCC) $(GENCODE) -shared -o $@ $(OBJS) -lm
+	$(NVCC) $(GENCODE) -shared -o $@ $(OBJS) -lm -ldl
 
 bin/raytracing: $(BUILD)/main.o $(LIB)
 	$(CC) -o $@ $(BUILD)/main.o -L$(PKG) -lraytracing_b200 -Wl,-rpath,'$$ORIGIN/../$(PKG)' -lm

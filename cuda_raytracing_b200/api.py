@@ -14,6 +14,7 @@ LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "libraytracing_b
 RT_TRAVERSAL_AUTO, RT_TRAVERSAL_REFERENCE, RT_TRAVERSAL_FAST = 0, 1, 2
 RT_RENDER_OUTPUT_SUM, RT_RENDER_NO_RNG_CACHE, RT_RENDER_COUNT_RAYS, RT_RENDER_COUNT_OPS, RT_RENDER_RESUME = 1, 2, 4, 8, 16
 RT_RENDER_FORWARD_THROUGHPUT = 32
+RT_SHARD_TILES, RT_SHARD_SAMPLES = 0, 1
 OP_NAMES = ["box", "sphere", "planar", "translation", "rotation", "lambert", "metal", "glass", "light", "noise", "checker", "arena"]
 
 
@@ -84,6 +85,12 @@ class PackInfo(C.Structure):  # rt_pack_info
                                           "program_wrappers")]
 
 
+class RenderPlan(C.Structure):  # rt_render_plan
+    _fields_ = [("kernel_mode", C.c_uint32), ("resident_lanes", C.c_uint32), ("chunk_count", C.c_uint32),
+                ("chunk_samples", C.c_int32), ("chunk_begin", C.c_int32 * 17), ("claim_group", C.c_uint32),
+                ("scattered", C.c_uint32)]
+
+
 class ProbeHit(C.Structure):  # rt_probe_hit
     _fields_ = [("origin", C.c_float * 3), ("direction", C.c_float * 3), ("point", C.c_float * 3),
                 ("normal", C.c_float * 3), ("t", C.c_float), ("u", C.c_float), ("v", C.c_float),
@@ -95,7 +102,8 @@ EXPORTS = [
     "rt_context_create", "rt_context_destroy", "rt_last_error_string", "rt_context_set_stream", "rt_context_reset_stream", "rt_scene_upload",
     "rt_render_params_from_camera", "rt_render_device", "rt_resolve_device", "rt_render", "rt_synchronize",
     "rt_render_state_save", "rt_render_state_load",
-    "rt_scene_pack_info", "rt_scene_program", "rt_render_world", "rt_probe_trace", "rt_probe_scatter", "rt_probe_texture", "rt_probe_xorwow",
+    "rt_group_create", "rt_group_destroy", "rt_group_size", "rt_group_context", "rt_group_last_error", "rt_group_render_world",
+    "rt_scene_pack_info", "rt_render_plan_query", "rt_scene_program", "rt_render_world", "rt_probe_trace", "rt_probe_scatter", "rt_probe_texture", "rt_probe_xorwow",
     # rt_scene.h
     "rt_world_init", "rt_world_free", "rt_mat_lambert_solid", "rt_mat_light_solid", "rt_mat_lambert_image",
     "rt_mat_lambert_image_pixels",
@@ -131,11 +139,22 @@ def lib():
         L.rt_render.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.POINTER(Stats)]
         L.rt_synchronize.argtypes = [C.c_void_p]
         L.rt_scene_pack_info.argtypes = [C.POINTER(SceneDesc), C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(PackInfo)]
+        L.rt_render_plan_query.argtypes = [C.POINTER(PackInfo), C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(RenderPlan)]
         L.rt_scene_program.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]
         L.rt_render_state_save.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.rt_render_state_load.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_uint64]
         L.rt_render_world.argtypes = [C.c_void_p, C.POINTER(World), C.POINTER(RenderSettings), C.c_uint32, C.c_void_p,
                                       C.c_void_p, C.POINTER(Stats)]
+        L.rt_group_create.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]
+        L.rt_group_destroy.argtypes = [C.c_void_p]
+        L.rt_group_destroy.restype = None
+        L.rt_group_size.argtypes = [C.c_void_p]
+        L.rt_group_context.argtypes = [C.c_void_p, C.c_int]
+        L.rt_group_context.restype = C.c_void_p
+        L.rt_group_last_error.argtypes = [C.c_void_p]
+        L.rt_group_last_error.restype = C.c_char_p
+        L.rt_group_render_world.argtypes = [C.c_void_p, C.POINTER(World), C.POINTER(RenderSettings), C.c_uint32, C.c_uint32,
+                                            C.c_void_p, C.c_void_p, C.POINTER(Stats)]
         L.rt_probe_trace.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_float,
                                      C.c_void_p]
         L.rt_probe_scatter.argtypes = [C.c_void_p, C.c_uint64] + [C.c_void_p] * 8
@@ -252,6 +271,15 @@ class HostScene:
         if rc != 0:
             raise RtError("rt_scene_pack_info: %d %s" % (rc, (lib().rt_last_error_string(None) or b"").decode()))
         return info
+
+    def render_plan(self, width=0, spp=0, bounces=0, sm_count=148, traversal=RT_TRAVERSAL_AUTO, rows=0):
+        """The scheduling decisions of a render of this scene (host only, no GPU needed)."""
+        s, cam = self.camera(width, spp, bounces)
+        info = self.pack_info(traversal)
+        plan = RenderPlan()
+        _check(lib().rt_render_plan_query(C.byref(info), cam.img_width, rows or cam.img_height, s.samples_per_pixel, s.max_bounces,
+                                          sm_count, C.byref(plan)))
+        return plan
 
     def program(self):
         """The linear program of the scene's reference-order walk (host only): uint32 view, shape (ops, 8); empty if none."""
@@ -387,6 +415,40 @@ class Context:
         out = np.empty((n, 6), np.uint32)
         _check(lib().rt_probe_xorwow(self._h, seed, first_subsequence, n, out.ctypes.data), self._h)
         return out
+
+
+class Group:
+    """rt_group: several GPUs of one box behind one call (NCCL reduce onto device 0 inside the library)."""
+
+    def __init__(self, devices):
+        ids = list(range(devices)) if isinstance(devices, int) else list(devices)
+        arr = (C.c_int * len(ids))(*ids)
+        self._h = C.c_void_p()
+        _check(lib().rt_group_create(arr, len(ids), C.byref(self._h)))
+        self.devices = ids
+
+    def close(self):
+        if self._h:
+            lib().rt_group_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def render_world(self, scene, settings=None, traversal=RT_TRAVERSAL_AUTO, shard=RT_SHARD_TILES):
+        s = settings if settings is not None else scene.settings
+        cam = Camera()
+        lib().rt_camera_setup(C.byref(s), C.byref(cam))
+        f = np.empty((cam.img_height, cam.img_width, 3), dtype=np.float32)
+        b = np.empty((cam.img_height, cam.img_width, 3), dtype=np.uint8)
+        st = Stats()
+        rc = lib().rt_group_render_world(self._h, C.byref(scene.world), C.byref(s), traversal, shard, f.ctypes.data, b.ctypes.data, C.byref(st))
+        if rc != 0:
+            raise RtError("rt error %d: %s" % (rc, (lib().rt_group_last_error(self._h) or b"?").decode()))
+        return f, b, st
 
 
 def write_ppm(path, rgb8):

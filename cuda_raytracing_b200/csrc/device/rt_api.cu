@@ -12,32 +12,13 @@
 #include <string>
 #include <vector>
 
-#include "rt_device.h"
-#include "rt_kernels.h"
-#include "rt_pack.h"
+#include "rt_context.h"
 
 namespace {
 
 thread_local std::string g_last_error;     // per host thread: contexts used from different threads do not share it
 
-struct DeviceBuffer {
-  void *ptr = nullptr; size_t bytes = 0;
-  cudaError_t upload(const void *src, size_t n, cudaStream_t s) {
-    release();
-    bytes = n;
-    if (n == 0) { return cudaMalloc(&ptr, 16); }                 // keep pointers valid for empty tables
-    cudaError_t e = cudaMalloc(&ptr, n);
-    if (e != cudaSuccess) return e;
-    return cudaMemcpyAsync(ptr, src, n, cudaMemcpyHostToDevice, s);
-  }
-  cudaError_t reserve(size_t n) {
-    if (n <= bytes && ptr) return cudaSuccess;
-    release();
-    bytes = n;
-    return cudaMalloc(&ptr, n ? n : 16);
-  }
-  void release() { if (ptr) cudaFree(ptr); ptr = nullptr; bytes = 0; }
-};
+using rtc::DeviceBuffer;
 
 double now_ms() {
   return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
@@ -48,39 +29,12 @@ cudaError_t to_device(DeviceBuffer &b, const T *src, size_t count, cudaStream_t 
 
 }  // namespace
 
-struct rt_context {
-  int device = 0, sm_count = 0;
-  cudaStream_t own_stream = nullptr, stream = nullptr;
-  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
-  std::string error;
-  // scene
-  bool has_scene = false;
-  rtd::Scene scene{};
-  rtp::PackedScene packed;
-  DeviceBuffer b_ref_nodes, b_xforms, b_instances, b_structs, b_struct_children, b_fast_nodes, b_spheres, b_planars, b_materials,
-      b_checkers, b_perlin_vec, b_perlin_perm, b_arena, b_program;
-  // rng
-  DeviceBuffer b_rng_mats, b_rng_init, b_rng_states, b_progress, b_counters;   // b_rng_init: pristine states (cache)
-  int chunk_samples = 0;                                   // 0 = automatic; env RT_CHUNK overrides (tuning knob)
-  int claim_group = 0;                                     // 0 = automatic; env RT_CLAIM_GROUP (tuning knob)
-  uint32_t fuse_min = 8;                                   // env RT_FUSE_MIN: wrapper chains around one object become one item when there are this many (0 = never)
-  uint32_t treelet_min = 8;                                // env RT_TREELET_MIN: smallest wrapper-free subtree given an own BVH (0 = none)
-  int tile_w = 8;                                          // work items walk 8x4-pixel tiles; env RT_TILE_W (1..32, power of 2)
-  int linear = -1;                                         // small scenes with wrappers walk their linear program (kernel mode 3): -1 / 1 yes, 0 never; env RT_LINEAR
-  int flat = -1;                                           // tiny scenes without wrappers skip their BVH (kernel mode 5): -1 / 1 yes, 0 never; env RT_FLAT
-  int scatter = -1;                                        // item order: -1 automatic, 0 tile order, 1 scattered; env RT_SCATTER
-  uint64_t rng_seed = 0, rng_first = 0, rng_count = 0, rng_bands = 0; bool rng_valid = false;   // what b_rng_init holds
-  uint64_t live_seed = 0, live_first = 0, live_count = 0, live_bands = 0; bool live_valid = false;  // what b_rng_states carries on from
-  // scratch for rt_render (host-buffer path)
-  DeviceBuffer b_pixels, b_rgb8;
-  rtk::LaunchInfo last_launch{};
-};
-
-static int fail(rt_context *ctx, int code, const std::string &msg) {
+int rtc::fail(rt_context *ctx, int code, const std::string &msg) {
   g_last_error = msg;
   if (ctx) ctx->error = msg;
   return code;
 }
+using rtc::fail;
 static int cuda_fail(rt_context *ctx, cudaError_t e, const char *what) {
   return fail(ctx, RT_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
 }
@@ -163,13 +117,20 @@ int rt_synchronize(rt_context *ctx) {
 
 int rt_scene_upload(rt_context *ctx, const rt_scene_desc *desc, uint32_t traversal) {
   if (!ctx || !desc) return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: NULL argument");
+  rtp::PackedScene p;
+  int rc = rtp::pack_scene(*desc, traversal, p, ctx->treelet_min, ctx->fuse_min, ctx->linear == 0 ? 0u : rtp::PROGRAM_MAX_DEFAULT);
+  if (rc != RT_OK) { ctx->has_scene = false; return fail(ctx, rc, p.error); }
+  return rtc::upload_packed(ctx, p);
+}
+
+}  // extern "C"
+
+int rtc::upload_packed(rt_context *ctx, const rtp::PackedScene &packed) {
   RT_CUDA(ctx, cudaSetDevice(ctx->device));
   ctx->has_scene = false;
   ctx->live_valid = false;                                 // parked XORWOW states belong to the scene they were rendered with
-  ctx->packed = rtp::PackedScene();
+  ctx->packed = packed;
   rtp::PackedScene &p = ctx->packed;
-  int rc = rtp::pack_scene(*desc, traversal, p, ctx->treelet_min, ctx->fuse_min, ctx->linear == 0 ? 0u : rtp::PROGRAM_MAX_DEFAULT);
-  if (rc != RT_OK) return fail(ctx, rc, p.error);
   if (ctx->flat == 0) p.flat = false;
   cudaStream_t s = ctx->stream;
 #define UP(buf, vec) RT_CUDA(ctx, ctx->buf.upload((vec).data(), (vec).size() * sizeof((vec)[0]), s))
@@ -198,6 +159,8 @@ int rt_scene_upload(rt_context *ctx, const rt_scene_desc *desc, uint32_t travers
   ctx->has_scene = true;
   return RT_OK;
 }
+
+extern "C" {
 
 // kernel variant: 1 = own BVH over the whole scene, 5 = tiny scene without wrappers (every primitive, no BVH),
 // 3 = reference order as a linear program (small scenes with wrappers), 2 = reference order with treelets / fused
@@ -256,6 +219,73 @@ static int render_set(rt_context *ctx, const rt_render_params *p, int row0, int 
                                     0x9e3779b97f4a7c15ull * (((uint64_t)(uint32_t)p->img_width << 32) | (uint32_t)p->img_height)
                               : 0;
   return RT_OK;
+}
+
+// ---- the scheduling decisions of a render: host logic only, shared by rt_render_device and rt_render_plan_query ----
+struct PlanKnobs { int chunk_samples = 0, claim_group = 0, scatter = -1, tile_w = 8; };
+static void plan_render(int packed_mode, uint32_t traversal_used, uint32_t prims, int32_t img_width, uint32_t rows, int32_t samples_per_pixel,
+                        int bounces, int sm_count, const PlanKnobs &kn, rt_render_plan *out) {
+  memset(out, 0, sizeof(*out));
+  int mode = packed_mode;
+  const uint64_t count = (uint64_t)rows * (uint64_t)img_width;
+  const int spp = samples_per_pixel > 0 ? samples_per_pixel : 1;
+  const long long life = (long long)spp * (long long)(bounces > 0 ? bounces : 1);       // bounces of a pixel's whole life, at most
+  // short-lived pixels (the regime that gets no time slices either) on the stackless walk: the 5 x 96-register build
+  if (mode == 3 && bounces <= 64 && life <= 256) mode = 4;
+  const double lanes = (double)sm_count * (mode == 3 ? 1024.0 : ((mode == 1 || mode == 5) ? 768.0 : 640.0));   // resident threads: 8, 6 or 5 blocks of 128 per SM
+  out->kernel_mode = (uint32_t)mode;
+  out->resident_lanes = (uint32_t)lanes;
+  // measured (profiles/r1_sweep_chunk_group.jsonl): big own-BVH scenes gain from claiming a whole warp of adjacent
+  // pixels at once (coherent node visits), small scenes and the reference-order walk from claiming at once
+  const bool big_fast = traversal_used == RT_TRAVERSAL_FAST && prims >= 64;
+  out->claim_group = (uint32_t)(kn.claim_group > 0 ? kn.claim_group : (big_fast ? 32 : 1));
+  // Item order (measured, profiles/r1_item_order_scatter.jsonl).  Tile order keeps neighbouring pixels in one warp and
+  // neighbouring tiles on one SM (coherent walks, L1 hits): scattering costs C1 +40 %, C2 +70 %, scene 3 at 4K +34 %.
+  // It pays where the render is short and bound by WHERE its slow pixels sit rather than by throughput:
+  //  (a) a tiny image (every pixel resident at once, <= 2 per lane): the slow pixels otherwise fill whole warps whose
+  //      every bounce then carries 32 Perlin evaluations (scene 17 at 400x400: 29.8 -> 27.2 ms with 4 time slices per
+  //      pixel instead of 24 -- spreading the pixels already does what the many slices did);
+  //  (b) the hybrid walk on a short render (scene 3 at 800x800: s16 136 -> 108 ms, s64 412 -> 390 ms): in tile order the
+  //      queue ends with the image's heaviest rows.
+  const uint32_t tw = (uint32_t)kn.tile_w, th = 32u / tw;
+  const uint32_t slots = (((uint32_t)img_width + tw - 1) / tw) * ((rows + th - 1) / th) * 32u;
+  const bool tiny_image = out->claim_group == 1 && (double)count <= 2.0 * lanes;
+  const bool short_hybrid = mode == 2 && count <= (1u << 20) && (double)spp * (double)count <= 1024.0 * lanes;
+  out->scattered = ((kn.scatter >= 0 ? kn.scatter == 1 : (tiny_image || short_hybrid)) && slots >= 64) ? 1u : 0u;
+
+  // Chunks.  A pixel's samples are produced in order, a chunk at a time; between chunks its XORWOW state and running sum
+  // are parked, so the render ends one CHUNK after the last claim, not one pixel.  Every hand-over costs a few iterations
+  // (and a lane waits when the chunk before is still in flight), so chunks should be few and long while there is plenty
+  // of work and short only at the end: sizes halve from spp / 2 down to ~1/256 of a resident lane's share of the render
+  // (never below 8 samples).  Measured on the Cornell box (profiles/r2a_c4_spp_chunk_prefetch_forward.jsonl): at s128
+  // 15 uniform chunks of 9 samples 46.8 ms, 4 of 32 samples 44.0 ms, 1 of 128 52.4 ms.
+  if (samples_per_pixel <= 0) { out->chunk_samples = 1; out->chunk_count = 1; return; }   // spp <= 0: the kernel writes 0 * scale
+  if (kn.chunk_samples > 0) {                              // RT_CHUNK: uniform chunks of that many samples
+    const int c = kn.chunk_samples < spp ? kn.chunk_samples : spp;
+    out->chunk_samples = c;
+    out->chunk_count = (uint32_t)((spp + c - 1) / c);
+    return;
+  }
+  const double per_lane = (double)spp * (double)count / lanes;
+  int tail = (int)(per_lane / 256.0);
+  if (tail < 8) tail = 8;
+  // a pixel whose whole life is at most a few hundred bounces has no tail worth slicing: parking its state costs
+  // more (C1, s16 b8: 1.31 -> 1.18 ms without slices; scene 3 at s16 b50 needs them: 143 vs 184 ms)
+  if (life <= 256 || tail >= spp) tail = spp;
+  int n = 0, done = 0;
+  out->chunk_begin[0] = 0;
+  if (tail >= spp) {                                       // one chunk: nothing to slice
+    out->chunk_begin[++n] = spp;
+  } else if (out->scattered && tiny_image && kn.scatter < 0) {   // tiny image in scattered order: 4 equal slices (see (a) above)
+    const int c = (spp + 3) / 4 > 8 ? (spp + 3) / 4 : 8;
+    while (done < spp) { done = done + c < spp ? done + c : spp; out->chunk_begin[++n] = done; }
+  } else {
+    while (spp - done > 2 * tail && n < rtd::MAX_CHUNK_TABLE - 2) { done += (spp - done + 1) / 2; out->chunk_begin[++n] = done; }
+    if (spp - done > tail && n < rtd::MAX_CHUNK_TABLE - 1) { done += (spp - done + 1) / 2; out->chunk_begin[++n] = done; }
+    if (spp - done > 0) { done = spp; out->chunk_begin[++n] = done; }
+  }
+  out->chunk_count = (uint32_t)n;
+  for (int k = n + 1; k <= rtd::MAX_CHUNK_TABLE; ++k) out->chunk_begin[k] = spp;
 }
 
 int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels, rt_stats *stats) {
@@ -319,58 +349,26 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   a.pixels = d_pixels;
   a.rng_states = (uint32_t *)ctx->b_rng_states.ptr;
   a.progress = (uint32_t *)ctx->b_progress.ptr;
-  int mode = kernel_mode(ctx->packed);
   const int bounces = p->max_bounces & 255;                // u8 counter of the reference (rt.cu:220)
-  // short-lived pixels (the regime that gets no time slices either) on the stackless walk: the 5 x 96-register build
-  if (mode == 3 && bounces <= 64 && (long long)p->samples_per_pixel * (long long)(bounces > 0 ? bounces : 1) <= 256) mode = 4;
-  const double lanes = (double)ctx->sm_count * (mode == 3 ? 1024.0 : ((mode == 1 || mode == 5) ? 768.0 : 640.0));   // resident threads: 8, 6 or 5 blocks of 128 per SM
-  {   // chunk size: about 1/32 of the samples one resident lane will produce, so that the tail of the render (lanes
-      // idle because every remaining pixel is owned) is a few per cent; never below 8 samples per claim
-    const int spp = p->samples_per_pixel > 0 ? p->samples_per_pixel : 1;
-    int chunk = ctx->chunk_samples;
-    if (chunk <= 0) {
-      const double per_lane = (double)spp * (double)count / lanes;
-      chunk = (int)(per_lane / 32.0);
-      if (chunk < 8) chunk = 8;
-      // a pixel whose whole life is at most a few hundred bounces has no tail worth slicing: parking its state costs
-      // more (C1, s16 b8: 1.31 -> 1.18 ms without slices; scene 3 at s16 b50 needs them: 143 vs 184 ms)
-      if ((long long)spp * (long long)(bounces > 0 ? bounces : 1) <= 256) chunk = spp;
-    }
-    if (chunk > spp) chunk = spp;
-    a.chunk_samples = chunk;
-    a.chunk_count = (spp + chunk - 1) / chunk;
-    const uint32_t tw = (uint32_t)ctx->tile_w, th = 32u / tw, rows = set_rows;
+  PlanKnobs knobs;
+  knobs.chunk_samples = ctx->chunk_samples; knobs.claim_group = ctx->claim_group; knobs.scatter = ctx->scatter; knobs.tile_w = ctx->tile_w;
+  rt_render_plan plan;
+  plan_render(kernel_mode(ctx->packed), ctx->packed.traversal_used, ctx->packed.sphere_count + ctx->packed.planar_count, p->img_width, set_rows,
+              p->samples_per_pixel, bounces, ctx->sm_count, knobs, &plan);
+  const int mode = (int)plan.kernel_mode;
+  a.chunk_samples = plan.chunk_samples;
+  a.chunk_count = (int32_t)plan.chunk_count;
+  for (int k = 0; k <= rtd::MAX_CHUNK_TABLE; ++k) a.chunk_begin[k] = plan.chunk_begin[k];
+  a.claim_group = (int32_t)plan.claim_group;
+  {
+    const uint32_t tw = (uint32_t)ctx->tile_w, th = 32u / tw;
     a.tile_shift = 0; while ((1u << a.tile_shift) < tw) ++a.tile_shift;
     a.first_row = row0;
     if (banded) { a.band_rows = (int32_t)p->band_rows; a.band_period = (int32_t)p->band_period; a.band_phase = (int32_t)p->band_phase; }
     a.tiles_x = ((uint32_t)p->img_width + tw - 1) / tw;
-    a.slots_per_chunk = a.tiles_x * ((rows + th - 1) / th) * 32u;
+    a.slots_per_chunk = a.tiles_x * ((set_rows + th - 1) / th) * 32u;
     a.item_count = (unsigned long long)a.slots_per_chunk * (unsigned long long)a.chunk_count;
-    // measured (profiles/r1_sweep_chunk_group.jsonl): big own-BVH scenes gain from claiming a whole warp of adjacent
-    // pixels at once (coherent node visits), small scenes and the reference-order walk from claiming at once
-    const bool big_fast = ctx->packed.traversal_used == RT_TRAVERSAL_FAST && ctx->packed.sphere_count + ctx->packed.planar_count >= 64;
-    a.claim_group = ctx->claim_group > 0 ? ctx->claim_group : (big_fast ? 32 : 1);
-    // Item order (measured, profiles/r1_item_order_scatter.jsonl).  Tile order keeps neighbouring pixels in one warp and
-    // neighbouring tiles on one SM (coherent walks, L1 hits): scattering costs C1 +40 %, C2 +70 %, scene 3 at 4K +34 %.
-    // It pays where the render is short and bound by WHERE its slow pixels sit rather than by throughput:
-    //  (a) a tiny image (every pixel resident at once, <= 2 per lane): the slow pixels otherwise fill whole warps whose
-    //      every bounce then carries 32 Perlin evaluations (scene 17 at 400x400: 29.8 -> 27.2 ms with 4 time slices per
-    //      pixel instead of 24 -- spreading the pixels already does what the many slices did);
-    //  (b) the hybrid walk on a short render (scene 3 at 800x800: s16 136 -> 108 ms, s64 412 -> 390 ms): in tile order the
-    //      queue ends with the image's heaviest rows.
-    // Multiplier: golden-ratio stride, coprime to the slot count, so slot -> slot * mul mod n is a permutation and
-    // neighbours in the queue are far apart in the image.
-    const bool tiny_image = a.claim_group == 1 && (double)count <= 2.0 * lanes;
-    const bool short_hybrid = mode == 2 && count <= (1u << 20) && (double)spp * (double)count <= 1024.0 * lanes;
-    const bool want_scatter = ctx->scatter >= 0 ? ctx->scatter == 1 : (tiny_image || short_hybrid);
-    if (want_scatter && a.slots_per_chunk >= 64) {
-      a.scatter_mul = scatter_multiplier(a.slots_per_chunk);
-      if (ctx->chunk_samples <= 0 && tiny_image && ctx->scatter < 0 && a.chunk_samples < (spp + 3) / 4) {   // at most 4 slices
-        a.chunk_samples = (spp + 3) / 4;
-        a.chunk_count = (spp + a.chunk_samples - 1) / a.chunk_samples;
-        a.item_count = (unsigned long long)a.slots_per_chunk * (unsigned long long)a.chunk_count;
-      }
-    }
+    if (plan.scattered) a.scatter_mul = scatter_multiplier(a.slots_per_chunk);
   }
   a.counters = (unsigned long long *)ctx->b_counters.ptr;
   a.stack_entries = (int32_t)ctx->scene.stack_entries;
@@ -557,6 +555,15 @@ int rt_probe_texture(rt_context *ctx, uint64_t n, uint64_t texture_offset, const
   if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   bu.release(); bp.release(); bo.release();
   if (e != cudaSuccess) return cuda_fail(ctx, e, "rt_probe_texture");
+  return RT_OK;
+}
+
+int rt_render_plan_query(const rt_pack_info *scene, int32_t img_width, int32_t rows, int32_t samples_per_pixel, int32_t max_bounces,
+                         int32_t sm_count, rt_render_plan *out) {
+  if (!scene || !out || img_width <= 0 || rows <= 0 || sm_count <= 0 || max_bounces < 0)
+    return fail(nullptr, RT_ERR_INVALID, "rt_render_plan_query: bad argument");
+  plan_render((int)scene->kernel_mode, scene->traversal_used, scene->spheres + scene->planars, img_width, (uint32_t)rows, samples_per_pixel,
+              max_bounces & 255, sm_count, PlanKnobs(), out);
   return RT_OK;
 }
 

@@ -95,6 +95,8 @@ struct Scene {
   uint64_t tex_bytes;
 };
 
+constexpr int MAX_CHUNK_TABLE = 16;
+
 struct RenderArgs {
   Scene scene;
   float *pixels;                // img_width*img_height*3 f32 (device)
@@ -109,7 +111,9 @@ struct RenderArgs {
   int32_t first_row;            // first_pixel / img_width
   int32_t band_rows, band_period, band_phase;   // band_rows > 0: row y of the rendered set is image row
                                 // ((y / band_rows) * band_period + band_phase) * band_rows + y % band_rows (interleaved bands)
-  int32_t chunk_samples, chunk_count;   // a pixel's samples are produced in order, chunk_samples at a time
+  int32_t chunk_samples, chunk_count;   // a pixel's samples are produced in order, a chunk at a time: chunk_samples each
+                                // (uniform), or -- chunk_samples == 0 -- samples [chunk_begin[k], chunk_begin[k + 1]) for chunk k
+  int32_t chunk_begin[MAX_CHUNK_TABLE + 1];   // decreasing chunk sizes: big chunks while there is plenty of work, a short tail
   int32_t claim_group;          // idle lanes of a warp claim work items together, this many at a time
   int32_t stack_entries;        // traversal stack entries per thread that this scene needs (<= STACK_CAPACITY): sizes the shared memory
   int32_t img_width, img_height, samples_per_pixel, max_bounces;

@@ -192,8 +192,12 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
       rng.d = s0.x; rng.v0 = s0.y; rng.v1 = s1.x; rng.v2 = s1.y; rng.v3 = s2.x; rng.v4 = s2.y;
       float *out = a.pixels + 3 * image_pixel(a, pix);
       acc = (chunk || a.resume) ? v3(__ldcg(out), __ldcg(out + 1), __ldcg(out + 2)) : v3(0.0f, 0.0f, 0.0f);
-      const int done = chunk * a.chunk_samples;
-      samples_left = a.samples_per_pixel - done < a.chunk_samples ? a.samples_per_pixel - done : a.chunk_samples;
+      if (a.chunk_samples > 0) {
+        const int done = chunk * a.chunk_samples;
+        samples_left = a.samples_per_pixel - done < a.chunk_samples ? a.samples_per_pixel - done : a.chunk_samples;
+      } else {
+        samples_left = a.chunk_begin[chunk + 1] - a.chunk_begin[chunk];
+      }
       new_path = true;
       if (samples_left <= 0) {                      // spp <= 0: the reference writes 0 * scale
         out[0] = 0.0f; out[1] = 0.0f; out[2] = 0.0f;

@@ -138,6 +138,27 @@ int rt_render_state_load(rt_context *ctx, const rt_render_params *p, const void 
 int rt_render_world(rt_context *ctx, rt_world *world, const rt_render_settings *settings, uint32_t traversal,
                     float *h_pixels_rgb, uint8_t *h_rgb8, rt_stats *stats);
 
+/* ---- several GPUs of one box: one context per device inside, NCCL over NVLink for the one exchange ----
+ * The reference renders on the default device only (rt.cu:1722-1723, 1754); this is the same call on N devices.  One host
+ * thread drives all of them.  NCCL (libnccl.so.2) is bound at run time and only needed for n_devices > 1. */
+typedef struct rt_group rt_group;
+enum {
+  RT_SHARD_TILES = 0,     /* device g renders interleaved bands of rows with the reference's XORWOW stream: the image is
+                             byte-identical to the one-GPU image (tier 1 kept) */
+  RT_SHARD_SAMPLES = 1    /* device g renders its share of the samples of every pixel (subsequence = pixel + g * n_pixels):
+                             perfect load balance, statistical (tier-2) parity for n_devices > 1 */
+};
+int  rt_group_create(const int *device_ids, int n_devices, rt_group **out);   /* device_ids NULL: devices 0 .. n_devices-1 */
+void rt_group_destroy(rt_group *g);
+int  rt_group_size(const rt_group *g);
+rt_context *rt_group_context(rt_group *g, int index);     /* the context of device `index` (owned by the group) */
+const char *rt_group_last_error(const rt_group *g);
+/* rt_render_world() on every device of the group: scene packed once and uploaded to each, shards rendered concurrently,
+ * one ncclReduce(sum) onto device 0, resolve + download there.  stats: render_ms = slowest device (XORWOW init + render),
+ * total_ms = device 0's clock from the first launch to the resolved image (render + reduce + resolve). */
+int  rt_group_render_world(rt_group *g, rt_world *world, const rt_render_settings *settings, uint32_t traversal, uint32_t shard,
+                           float *h_pixels_rgb, uint8_t *h_rgb8, rt_stats *stats);
+
 /* ---- per-function probes used by the parity tests (same kernels' device functions, batch in / batch out) ---- */
 typedef struct rt_probe_hit {          /* one per ray; mirrors the reference's HitRecord fields + the mutated ray */
   float origin[3], direction[3];       /* ray AFTER traversal (instance wrappers edit it in place, Q12) */
@@ -168,6 +189,22 @@ typedef struct rt_pack_info {
   uint32_t program_boxes, program_prims, program_wrappers;   /* of which box tests, primitive tests, wrappers (ways in) */
 } rt_pack_info;
 int rt_scene_pack_info(const rt_scene_desc *scene, uint32_t traversal, uint32_t treelet_min, uint32_t fuse_min, rt_pack_info *out);
+
+/* The scheduling decisions rt_render_device takes for a render of `rows` rows of an img_width-wide image of that scene on a
+ * GPU with sm_count SMs (148 on a B200) -- host only, no CUDA call, no context (works without a GPU; environment knobs
+ * such as RT_CHUNK are not applied).  A pixel's samples are produced in order, a chunk at a time, by whichever lane
+ * claims the chunk; chunk sizes halve from spp / 2 down to a short tail. */
+typedef struct rt_render_plan {
+  uint32_t kernel_mode;                    /* rt_pack_info.kernel_mode after the short-lived-pixel rule (3 -> 4) */
+  uint32_t resident_lanes;                 /* threads the persistent grid keeps resident */
+  uint32_t chunk_count;
+  int32_t  chunk_samples;                  /* > 0: uniform chunks of that many samples; 0: the table below */
+  int32_t  chunk_begin[17];                /* chunk k renders samples [chunk_begin[k], chunk_begin[k + 1]) */
+  uint32_t claim_group;                    /* idle lanes of a warp claim work items together, this many at a time */
+  uint32_t scattered;                      /* item order: 0 tile order, 1 golden-ratio permutation of the queue */
+} rt_render_plan;
+int rt_render_plan_query(const rt_pack_info *scene, int32_t img_width, int32_t rows, int32_t samples_per_pixel, int32_t max_bounces,
+                         int32_t sm_count, rt_render_plan *out);
 
 /* The linear program RT_TRAVERSAL_AUTO would upload for `scene` (host only, no GPU needed), for inspection and tests:
  * 8 floats per op -- {x0,x1,y0,y1, z0,z1, skip op, K_BVH} for a box (a missed box continues at `skip`, every other op at

@@ -48,6 +48,15 @@ def test_no_gpu_fails_loudly(product_lib):
     assert "no CPU fallback" in str(e.value)
 
 
+def test_group_without_gpu_fails_loudly(product_lib):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(product_lib.RtError) as e:
+        product_lib.Group(2)
+    assert "no CPU fallback" in str(e.value)
+
+
 def test_product_does_not_link_oracle(product_lib):
     out = subprocess.run(["ldd", product_lib.LIB_PATH], capture_output=True, text=True).stdout
     assert "oracle" not in out and "libref_host" not in out

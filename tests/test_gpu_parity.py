@@ -579,3 +579,79 @@ def test_forward_throughput_mode_is_within_tolerance(gpu_ctx, oracle, product_li
     assert np.all(np.abs(fwd - exact) <= 1e-5 * np.abs(exact) + 1e-9), float(np.abs(fwd - exact).max())
     assert np.abs(f8.astype(np.int32) - e8.astype(np.int32)).max() <= 1
     hs.close()
+
+
+def _gpu_count():
+    import torch
+    return torch.cuda.device_count() if torch.cuda.is_available() else 0
+
+
+@pytest.mark.gpu
+def test_group_of_one_device_is_the_single_gpu_path(product_lib, oracle):
+    """rt_group with one device (no NCCL involved): rt_group_render_world == rt_render_world, bit for bit, for both
+    shardings (with one device there is nothing to deal out)."""
+    hs = product_lib.HostScene(1)
+    s, _ = hs.camera(96, 8, 12)
+    ctx = product_lib.Context(0)
+    want, want8, st0 = ctx.render_world(hs, s)
+    ctx.close()
+    grp = product_lib.Group(1)
+    for shard in (product_lib.RT_SHARD_TILES, product_lib.RT_SHARD_SAMPLES):
+        got, got8, st = grp.render_world(hs, s, shard=shard)
+        assert np.array_equal(common.bits(got), common.bits(want)) and np.array_equal(got8, want8)
+        assert st.paths == st0.paths and st.rays == st0.rays
+    grp.close()
+    hs.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sid", [1, 2, 3])
+def test_group_of_two_devices(product_lib, oracle, sid):
+    """Multi-GPU through the C ABI (rt_group: contexts + ncclCommInitAll + one ncclReduce onto device 0).  Tiles: the
+    2-GPU image is byte-identical to the 1-GPU image.  Samples: it is the sum of the two shard renders (device 0 carries
+    the reference's stream, device 1 subsequence pixel + n_pixels) scaled by 1/spp -- exactly what two virtual ranks on
+    one GPU produce."""
+    if _gpu_count() < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
+    hs = product_lib.HostScene(sid)
+    width, spp, b = 120, 10, 12
+    s, cam = hs.camera(width, spp, b)
+    ctx = product_lib.Context(0)
+    one, one8, st1 = ctx.render_world(hs, s)
+    grp = product_lib.Group(2)
+    tiles, tiles8, st = grp.render_world(hs, s, shard=product_lib.RT_SHARD_TILES)
+    assert np.array_equal(common.bits(tiles), common.bits(one)) and np.array_equal(tiles8, one8)
+    assert st.paths == st1.paths and st.rays == st1.rays
+    samp, samp8, st = grp.render_world(hs, s, shard=product_lib.RT_SHARD_SAMPLES)
+    n = cam.img_width * cam.img_height
+    ctx.upload(hs, product_lib.RT_TRAVERSAL_AUTO)
+    total = np.zeros_like(one)
+    rays = 0
+    for g in range(2):
+        q = hs.params(width, spp // 2, b, subsequence_offset=g * n, flags=product_lib.RT_RENDER_OUTPUT_SUM | product_lib.RT_RENDER_COUNT_RAYS)
+        part, _, sp = ctx.render(q)
+        total += part
+        rays += sp.rays
+    scale = np.float32(1.0) / np.float32(spp)
+    assert np.array_equal(common.bits(samp), common.bits(total * scale))
+    assert np.array_equal(samp8, oracle.resolve_rgb8(total * scale)) and st.rays == rays
+    grp.close(); ctx.close(); hs.close()
+
+
+@pytest.mark.gpu
+def test_cli_two_gpus_writes_the_same_file(product_lib):
+    if _gpu_count() < 2:
+        pytest.skip("needs two GPUs (run with gpurun --gpus 2)")
+    exe = os.path.join(common.ROOT, "bin", "raytracing")
+    with tempfile.TemporaryDirectory() as d:
+        outs = []
+        for extra in ([], ["g2"], ["g2", "d0"]):
+            sub = os.path.join(d, "run%d" % len(outs)); os.mkdir(sub)
+            r = subprocess.run([exe, "1", "s6", "b10", "w150"] + extra, cwd=sub, capture_output=True, text=True, timeout=600)
+            assert r.returncode == 0, r.stderr
+            assert r.stdout.splitlines()[0] == "cuda_calc launch error: no error"
+            outs.append(open(os.path.join(sub, "cornell_box.ppm"), "rb").read())
+        assert outs[0] == outs[1] == outs[2]
+        sub = os.path.join(d, "samples"); os.mkdir(sub)
+        r = subprocess.run([exe, "1", "s6", "b10", "w150", "g2", "d1"], cwd=sub, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0 and len(open(os.path.join(sub, "cornell_box.ppm"), "rb").read()) == len(outs[0])
