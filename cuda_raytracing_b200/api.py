@@ -87,7 +87,7 @@ class PackInfo(C.Structure):  # rt_pack_info
 
 class RenderPlan(C.Structure):  # rt_render_plan
     _fields_ = [("kernel_mode", C.c_uint32), ("resident_lanes", C.c_uint32), ("chunk_count", C.c_uint32),
-                ("chunk_samples", C.c_int32), ("chunk_begin", C.c_int32 * 17), ("claim_group", C.c_uint32),
+                ("chunk_samples", C.c_int32), ("chunk_begin", C.c_int32 * 33), ("claim_group", C.c_uint32),
                 ("scattered", C.c_uint32)]
 
 

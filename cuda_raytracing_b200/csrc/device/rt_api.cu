@@ -254,11 +254,14 @@ static void plan_render(int packed_mode, uint32_t traversal_used, uint32_t prims
   out->scattered = ((kn.scatter >= 0 ? kn.scatter == 1 : (tiny_image || short_hybrid)) && slots >= 64) ? 1u : 0u;
 
   // Chunks.  A pixel's samples are produced in order, a chunk at a time; between chunks its XORWOW state and running sum
-  // are parked, so the render ends one CHUNK after the last claim, not one pixel.  Every hand-over costs a few iterations
-  // (and a lane waits when the chunk before is still in flight), so chunks should be few and long while there is plenty
-  // of work and short only at the end: sizes halve from spp / 2 down to ~1/256 of a resident lane's share of the render
-  // (never below 8 samples).  Measured on the Cornell box (profiles/r2a_c4_spp_chunk_prefetch_forward.jsonl): at s128
-  // 15 uniform chunks of 9 samples 46.8 ms, 4 of 32 samples 44.0 ms, 1 of 128 52.4 ms.
+  // are parked, so the render ends one CHUNK after the last claim, not one pixel.  Measured on the Cornell box
+  // (profiles/r2a_c4_spp_chunk_prefetch_forward.jsonl, r2b_chunk_schedules.jsonl):
+  //  * a hand-over costs a few iterations, so chunks below ~32 samples hurt (s128: 15 chunks of 9 samples 46.8 ms, 4 of 32
+  //    44.0 ms) -- except where a pixel's samples are few and heavy (scene 3 at s16 needs its two chunks of 8);
+  //  * chunks of more than ~1/16 of a resident lane's share of the render hurt too: a slow pixel's next chunk is claimed
+  //    long before this one is done and the claimer waits (s1024: 14 chunks of 76 samples 318 ms, halving from 512 down
+  //    340 ms; s128 as one chunk 52.4 ms);
+  //  * so: equal chunks of 1/32 of a lane's share for the bulk, then halving ones down to 8 samples for the tail.
   if (samples_per_pixel <= 0) { out->chunk_samples = 1; out->chunk_count = 1; return; }   // spp <= 0: the kernel writes 0 * scale
   if (kn.chunk_samples > 0) {                              // RT_CHUNK: uniform chunks of that many samples
     const int c = kn.chunk_samples < spp ? kn.chunk_samples : spp;
@@ -267,21 +270,23 @@ static void plan_render(int packed_mode, uint32_t traversal_used, uint32_t prims
     return;
   }
   const double per_lane = (double)spp * (double)count / lanes;
-  int tail = (int)(per_lane / 256.0);
-  if (tail < 8) tail = 8;
+  int bulk = (int)(per_lane / 32.0);
+  const int floor_c = spp / 2 < 8 ? 8 : (spp / 2 < 32 ? spp / 2 : 32);
+  if (bulk < floor_c) bulk = floor_c;
+  if (bulk < (spp + 23) / 24) bulk = (spp + 23) / 24;      // at most 24 equal chunks + the tail: the table holds 32
   // a pixel whose whole life is at most a few hundred bounces has no tail worth slicing: parking its state costs
   // more (C1, s16 b8: 1.31 -> 1.18 ms without slices; scene 3 at s16 b50 needs them: 143 vs 184 ms)
-  if (life <= 256 || tail >= spp) tail = spp;
+  if (life <= 256 || bulk >= spp) bulk = spp;
   int n = 0, done = 0;
   out->chunk_begin[0] = 0;
-  if (tail >= spp) {                                       // one chunk: nothing to slice
+  if (bulk >= spp) {                                       // one chunk: nothing to slice
     out->chunk_begin[++n] = spp;
   } else if (out->scattered && tiny_image && kn.scatter < 0) {   // tiny image in scattered order: 4 equal slices (see (a) above)
     const int c = (spp + 3) / 4 > 8 ? (spp + 3) / 4 : 8;
     while (done < spp) { done = done + c < spp ? done + c : spp; out->chunk_begin[++n] = done; }
   } else {
-    while (spp - done > 2 * tail && n < rtd::MAX_CHUNK_TABLE - 2) { done += (spp - done + 1) / 2; out->chunk_begin[++n] = done; }
-    if (spp - done > tail && n < rtd::MAX_CHUNK_TABLE - 1) { done += (spp - done + 1) / 2; out->chunk_begin[++n] = done; }
+    while (spp - done > 2 * bulk && n < rtd::MAX_CHUNK_TABLE - 6) { done += bulk; out->chunk_begin[++n] = done; }
+    while (spp - done >= 16 && n < rtd::MAX_CHUNK_TABLE - 1) { done += (spp - done + 1) / 2; out->chunk_begin[++n] = done; }
     if (spp - done > 0) { done = spp; out->chunk_begin[++n] = done; }
   }
   out->chunk_count = (uint32_t)n;

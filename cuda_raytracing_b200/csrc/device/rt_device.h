@@ -95,7 +95,7 @@ struct Scene {
   uint64_t tex_bytes;
 };
 
-constexpr int MAX_CHUNK_TABLE = 16;
+constexpr int MAX_CHUNK_TABLE = 32;
 
 struct RenderArgs {
   Scene scene;
@@ -113,7 +113,7 @@ struct RenderArgs {
                                 // ((y / band_rows) * band_period + band_phase) * band_rows + y % band_rows (interleaved bands)
   int32_t chunk_samples, chunk_count;   // a pixel's samples are produced in order, a chunk at a time: chunk_samples each
                                 // (uniform), or -- chunk_samples == 0 -- samples [chunk_begin[k], chunk_begin[k + 1]) for chunk k
-  int32_t chunk_begin[MAX_CHUNK_TABLE + 1];   // decreasing chunk sizes: big chunks while there is plenty of work, a short tail
+  int32_t chunk_begin[MAX_CHUNK_TABLE + 1];   // equal chunks for the bulk of the render, halving ones for its tail
   int32_t claim_group;          // idle lanes of a warp claim work items together, this many at a time
   int32_t stack_entries;        // traversal stack entries per thread that this scene needs (<= STACK_CAPACITY): sizes the shared memory
   int32_t img_width, img_height, samples_per_pixel, max_bounces;

@@ -193,13 +193,13 @@ int rt_scene_pack_info(const rt_scene_desc *scene, uint32_t traversal, uint32_t 
 /* The scheduling decisions rt_render_device takes for a render of `rows` rows of an img_width-wide image of that scene on a
  * GPU with sm_count SMs (148 on a B200) -- host only, no CUDA call, no context (works without a GPU; environment knobs
  * such as RT_CHUNK are not applied).  A pixel's samples are produced in order, a chunk at a time, by whichever lane
- * claims the chunk; chunk sizes halve from spp / 2 down to a short tail. */
+ * claims the chunk: equal chunks for the bulk of the render, halving ones for its tail. */
 typedef struct rt_render_plan {
   uint32_t kernel_mode;                    /* rt_pack_info.kernel_mode after the short-lived-pixel rule (3 -> 4) */
   uint32_t resident_lanes;                 /* threads the persistent grid keeps resident */
   uint32_t chunk_count;
   int32_t  chunk_samples;                  /* > 0: uniform chunks of that many samples; 0: the table below */
-  int32_t  chunk_begin[17];                /* chunk k renders samples [chunk_begin[k], chunk_begin[k + 1]) */
+  int32_t  chunk_begin[33];                /* chunk k renders samples [chunk_begin[k], chunk_begin[k + 1]) */
   uint32_t claim_group;                    /* idle lanes of a warp claim work items together, this many at a time */
   uint32_t scattered;                      /* item order: 0 tile order, 1 golden-ratio permutation of the queue */
 } rt_render_plan;

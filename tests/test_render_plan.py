@@ -17,7 +17,7 @@ def _plan(product_lib, name, **kw):
 @pytest.mark.parametrize("name", list(CONFIGS))
 def test_chunk_table_is_a_partition_of_the_samples(product_lib, name):
     pl, spp = _plan(product_lib, name)
-    assert pl.chunk_samples == 0 and 1 <= pl.chunk_count <= 16
+    assert pl.chunk_samples == 0 and 1 <= pl.chunk_count <= 32
     begin = list(pl.chunk_begin)
     assert begin[0] == 0 and begin[pl.chunk_count] == spp
     sizes = [begin[k + 1] - begin[k] for k in range(pl.chunk_count)]
@@ -32,11 +32,12 @@ def test_plans_of_the_baseline_configs(product_lib):
         pl, spp = _plan(product_lib, name)
         got[name] = (pl.kernel_mode, pl.resident_lanes, list(pl.chunk_begin)[:pl.chunk_count + 1], pl.claim_group, pl.scattered)
     assert got["C1"] == (4, 148 * 640, [0, 16], 1, 0)                        # short-lived pixels: 5 x 96 build, one chunk
-    assert got["C2"] == (1, 148 * 768, [0, 128, 192, 224, 240, 248, 256], 32, 0)
+    assert got["C2"] == (1, 148 * 768, [0, 57, 114, 171, 214, 235, 246, 256], 32, 0)
     assert got["C3"] == (5, 148 * 768, [0, 128, 256, 384, 512], 1, 1)        # tiny image: 4 equal slices, scattered order
-    assert got["C4"] == (3, 148 * 1024, [0, 512, 768, 896, 960, 992, 1008, 1016, 1024], 1, 0)
-    assert got["C4/8"] == (3, 148 * 1024, [0, 64, 96, 112, 120, 128], 1, 0)  # an 8-GPU share of C4: 5 chunks, 8-sample tail
-    assert got["C5r"] == (2, 148 * 640, [0, 8, 16], 1, 1)                    # short hybrid render: scattered
+    assert got["C4"][:2] == (3, 148 * 1024) and got["C4"][2][:13] == [76 * k for k in range(13)]   # 12 equal chunks of 1/32 of a lane's share ...
+    assert got["C4"][2][13:] == [968, 996, 1010, 1024]                       # ... then a halving tail
+    assert got["C4/8"] == (3, 148 * 1024, [0, 32, 64, 96, 112, 120, 128], 1, 0)   # an 8-GPU share of C4: never below 32 samples in the bulk
+    assert got["C5r"] == (2, 148 * 640, [0, 8, 16], 1, 1)                    # short hybrid render: two chunks of 8, scattered
     assert got["C5"][0] == 2 and got["C5"][4] == 0 and len(got["C5"][2]) <= 3
 
 
@@ -52,9 +53,9 @@ def test_plan_edge_cases(product_lib):
     assert list(pl.chunk_begin)[:2] == [0, 1] and pl.chunk_count == 1
     assert L.rt_render_plan_query(C.byref(info), 0, 675, 1, 50, 148, C.byref(pl)) != 0
     assert L.rt_render_plan_query(C.byref(info), 1200, 675, 1, -1, 148, C.byref(pl)) != 0
-    for spp in (7, 8, 9, 17, 100, 1000, 65536):                               # any spp: a partition, at most 16 chunks
+    for spp in (7, 8, 9, 17, 100, 1000, 65536):                               # any spp: a partition, at most 32 chunks
         assert L.rt_render_plan_query(C.byref(info), 64, 36, spp, 50, 148, C.byref(pl)) == 0
         b = list(pl.chunk_begin)
-        assert b[0] == 0 and b[pl.chunk_count] == spp and pl.chunk_count <= 16
+        assert b[0] == 0 and b[pl.chunk_count] == spp and pl.chunk_count <= 32
         assert all(b[k + 1] > b[k] for k in range(pl.chunk_count))
     hs.close()
