@@ -70,6 +70,7 @@ int rt_context_create(int device_id, rt_context **out) {
   if (const char *v = getenv("RT_LINEAR")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->linear = (int)x; }
   if (const char *v = getenv("RT_FLAT")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->flat = (int)x; }
   if (const char *v = getenv("RT_SCATTER")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->scatter = (int)x; }
+  if (const char *v = getenv("RT_FIRST_CHUNK")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 24)) ctx->first_chunk = (int)x; }
   if (const char *v = getenv("RT_CLAIM_GROUP")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= 32) ctx->claim_group = (int)x; }
   std::vector<uint32_t> mats;
   rtp::xorwow_sequence_matrices(mats);
@@ -222,7 +223,7 @@ static int render_set(rt_context *ctx, const rt_render_params *p, int row0, int 
 }
 
 // ---- the scheduling decisions of a render: host logic only, shared by rt_render_device and rt_render_plan_query ----
-struct PlanKnobs { int chunk_samples = 0, claim_group = 0, scatter = -1, tile_w = 8; };
+struct PlanKnobs { int chunk_samples = 0, claim_group = 0, scatter = -1, tile_w = 8, first_chunk = 0; };
 static void plan_render(int packed_mode, uint32_t traversal_used, uint32_t prims, int32_t img_width, uint32_t rows, int32_t samples_per_pixel,
                         int bounces, int sm_count, const PlanKnobs &kn, rt_render_plan *out) {
   memset(out, 0, sizeof(*out));
@@ -271,7 +272,10 @@ static void plan_render(int packed_mode, uint32_t traversal_used, uint32_t prims
   }
   const double per_lane = (double)spp * (double)count / lanes;
   int bulk = (int)(per_lane / 32.0);
-  const int floor_c = spp / 2 < 8 ? 8 : (spp / 2 < 32 ? spp / 2 : 32);
+  // the 32-sample floor is the Cornell box's (cheap iterations, many of them); the hybrid walk over the big scene wants its
+  // chunks short (scene 3 at s64: 13 samples 389 ms, 32 samples 409 ms), as before: never below 8
+  const int floor_want = (mode == 3 || mode == 4) ? 32 : 8;
+  const int floor_c = spp / 2 < 8 ? 8 : (spp / 2 < floor_want ? spp / 2 : floor_want);
   if (bulk < floor_c) bulk = floor_c;
   if (bulk < (spp + 23) / 24) bulk = (spp + 23) / 24;      // at most 24 equal chunks + the tail: the table holds 32
   // a pixel whose whole life is at most a few hundred bounces has no tail worth slicing: parking its state costs
@@ -285,6 +289,7 @@ static void plan_render(int packed_mode, uint32_t traversal_used, uint32_t prims
     const int c = (spp + 3) / 4 > 8 ? (spp + 3) / 4 : 8;
     while (done < spp) { done = done + c < spp ? done + c : spp; out->chunk_begin[++n] = done; }
   } else {
+    if (kn.first_chunk > 0 && kn.first_chunk < bulk) { done = kn.first_chunk; out->chunk_begin[++n] = done; }   // RT_FIRST_CHUNK (experiments)
     while (spp - done > 2 * bulk && n < rtd::MAX_CHUNK_TABLE - 6) { done += bulk; out->chunk_begin[++n] = done; }
     while (spp - done >= 16 && n < rtd::MAX_CHUNK_TABLE - 1) { done += (spp - done + 1) / 2; out->chunk_begin[++n] = done; }
     if (spp - done > 0) { done = spp; out->chunk_begin[++n] = done; }
@@ -357,6 +362,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   const int bounces = p->max_bounces & 255;                // u8 counter of the reference (rt.cu:220)
   PlanKnobs knobs;
   knobs.chunk_samples = ctx->chunk_samples; knobs.claim_group = ctx->claim_group; knobs.scatter = ctx->scatter; knobs.tile_w = ctx->tile_w;
+  knobs.first_chunk = ctx->first_chunk;
   rt_render_plan plan;
   plan_render(kernel_mode(ctx->packed), ctx->packed.traversal_used, ctx->packed.sphere_count + ctx->packed.planar_count, p->img_width, set_rows,
               p->samples_per_pixel, bounces, ctx->sm_count, knobs, &plan);

@@ -55,6 +55,7 @@ struct rt_context {
   rtc::DeviceBuffer b_rng_mats, b_rng_init, b_rng_states, b_progress, b_counters;   // b_rng_init: pristine states (cache)
   int chunk_samples = 0;                                   // 0 = automatic; env RT_CHUNK overrides (tuning knob)
   int claim_group = 0;                                     // 0 = automatic; env RT_CLAIM_GROUP (tuning knob)
+  int first_chunk = 0;                                     // env RT_FIRST_CHUNK: a short first chunk in front of the schedule (experiments)
   uint32_t fuse_min = 8;                                   // env RT_FUSE_MIN: wrapper chains around one object become one item when there are this many (0 = never)
   uint32_t treelet_min = 8;                                // env RT_TREELET_MIN: smallest wrapper-free subtree given an own BVH (0 = none)
   int tile_w = 8;                                          // work items walk 8x4-pixel tiles; env RT_TILE_W (1..32, power of 2)

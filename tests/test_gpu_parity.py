@@ -655,3 +655,43 @@ def test_cli_two_gpus_writes_the_same_file(product_lib):
         sub = os.path.join(d, "samples"); os.mkdir(sub)
         r = subprocess.run([exe, "1", "s6", "b10", "w150", "g2", "d1"], cwd=sub, capture_output=True, text=True, timeout=600)
         assert r.returncode == 0 and len(open(os.path.join(sub, "cornell_box.ppm"), "rb").read()) == len(outs[0])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sid", [3, 1, 0, 12])
+def test_fast_traversal_geometry_vs_oracle(gpu_ctx, oracle, product_lib, sid):
+    """RT_TRAVERSAL_FAST flattens instances to world space: its hits are not bit-identical to the reference's (which edits the
+    ray in place and undoes it inexactly), but they must be the SAME GEOMETRY -- same object hit or missed, t, point and
+    normal equal to rounding -- for primary rays and for bounce rays that start on the instanced objects."""
+    hs = product_lib.HostScene(sid)
+    sc = common.oracle_scene(oracle, hs)
+    L = oracle.lib()
+    rng = np.random.default_rng(900 + sid)
+    o, d, t = common.scene_rays(hs.settings, rng, 6000)
+    gpu_ctx.upload(hs, product_lib.RT_TRAVERSAL_REFERENCE)
+    first = gpu_ctx.probe_trace(o, d, t)
+    # second generation: lambertian bounces off whatever the first generation hit
+    idx = [i for i in range(len(first)) if first[i].hit][:4000]
+    o2 = np.array([first[i].point[:] for i in idx], np.float32)
+    u = rng.normal(size=(len(idx), 3)).astype(np.float32); u /= np.linalg.norm(u, axis=1, keepdims=True)
+    d2 = (np.array([first[i].normal[:] for i in idx], np.float32) + u).astype(np.float32)
+    t2 = rng.random(len(idx)).astype(np.float32)
+    O, D, T = np.concatenate([o, o2]), np.concatenate([d, d2]), np.concatenate([t, t2])
+    gpu_ctx.upload(hs, product_lib.RT_TRAVERSAL_FAST)
+    got = gpu_ctx.probe_trace(O, D, T)
+    bad = []
+    for i in range(len(O)):
+        oo, dd = O[i].copy(), D[i].copy()
+        rec = oracle.OrcHit()
+        h = L.orc_hit(C.byref(sc.c), oracle.fptr(oo), oracle.fptr(dd), float(T[i]), 0.001, float("inf"), C.byref(rec))
+        g = got[i]
+        if bool(g.hit) != bool(h):
+            bad.append((i, "hit", g.hit, h)); continue
+        if h:
+            scale = max(1.0, abs(rec.t))
+            if abs(g.t - rec.t) > 2e-3 * scale or np.abs(np.array(g.normal[:]) - np.array(rec.normal[:])).max() > 2e-2 \
+                    or g.material_type != rec.mat[0]:
+                bad.append((i, "rec", g.t, rec.t, list(g.normal[:]), list(rec.normal[:]), g.material_type, rec.mat[0]))
+    print("fast-vs-oracle geometry, scene %d: %d rays, %d differ: %s" % (sid, len(O), len(bad), bad[:6]))
+    assert len(bad) <= len(O) // 500, (sid, len(bad))           # grazing rays / ties may fall either way
+    hs.close()
