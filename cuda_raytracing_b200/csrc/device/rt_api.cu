@@ -594,6 +594,7 @@ int rt_scene_pack_info(const rt_scene_desc *scene, uint32_t traversal, uint32_t 
   out->stack_need = p.traversal_used == RT_TRAVERSAL_FAST ? p.fast_stack_need : p.ref_stack_need;
   out->stack_capacity = (uint32_t)rtd::STACK_CAPACITY;
   out->perlin_tables = p.perlin_tables; out->has_wrappers = p.has_wrappers ? 1u : 0u;
+  out->instanced_leaves = p.instanced_leaves;
   return RT_OK;
 }
 

@@ -97,7 +97,12 @@ static inline float box_area(const Box &b) {
 }
 // object -> world transform of a (translation o y-rotation)* chain: world = R(p) + T,
 // R: x = c*x' + s*z', z = -s*x' + c*z'   (the inverse of the ray rotation of rt.cu:1196-1206)
-struct Xf { float c = 1.0f, s = 0.0f; V t{0, 0, 0}; bool identity = true; };
+struct Xf {
+  float c = 1.0f, s = 0.0f; V t{0, 0, 0}; bool identity = true;
+  // the chain of wrappers as the reference would walk it, while it still has the shape [translation][y-rotation] (at most one
+  // of each, the translation outermost): such a primitive stays in its OWN space and is tested there (instanced leaf)
+  bool simple = true; uint32_t flags = 0; float off[3] = {0, 0, 0}, sn = 0.0f, cs = 1.0f;
+};
 static inline V xf_dir(const Xf &x, V p) { return V{x.c * p.x + x.s * p.z, p.y, -x.s * p.x + x.c * p.z}; }
 static inline V xf_point(const Xf &x, V p) { V r = xf_dir(x, p); return V{r.x + x.t.x, r.y + x.t.y, r.z + x.t.z}; }
 
@@ -419,7 +424,7 @@ struct Packer {
         else {
           V c = xf_point(xf, vv(h.u.sphere.center)), mv = xf_dir(xf, vv(h.u.sphere.direction));
           float r = h.u.sphere.radius, pad = 1e-4f * (1.0f + fabsf(r));
-          lf.ref = make_ref(K_SPHERE, add_sphere(c, mv, r, h.u.sphere.mat));
+          lf.ref = xf.simple ? instanced_leaf(xf, tag[href]) : make_ref(K_SPHERE, add_sphere(c, mv, r, h.u.sphere.mat));
           lf.box = box_empty();
           for (int e = 0; e < 2; ++e) {
             V p{c.x + e * mv.x, c.y + e * mv.y, c.z + e * mv.z};
@@ -442,7 +447,7 @@ struct Packer {
           g.w = rt_vec3{n.x * (1.0f / nn), n.y * (1.0f / nn), n.z * (1.0f / nn)};
           g.normal = len == 0.0f ? rt_vec3{0, 0, 0} : rt_vec3{n.x / len, n.y / len, n.z / len};
           g.d = g.normal.x * q.x + g.normal.y * q.y + g.normal.z * q.z;
-          lf.ref = make_ref(tri ? K_TRIANGLE : K_QUAD, add_planar(g, h.u.planar.mat));
+          lf.ref = xf.simple ? instanced_leaf(xf, tag[href]) : make_ref(tri ? K_TRIANGLE : K_QUAD, add_planar(g, h.u.planar.mat));
           lf.box = box_empty();
           box_point(lf.box, q); box_point(lf.box, V{q.x + u.x, q.y + u.y, q.z + u.z});
           box_point(lf.box, V{q.x + v.x, q.y + v.y, q.z + v.z});
@@ -457,11 +462,16 @@ struct Packer {
       case RT_OBJ_TRANSLATION: {
         Xf x = xf; V o = xf_dir(xf, vv(h.u.translation.offset));
         x.t = V{xf.t.x + o.x, xf.t.y + o.y, xf.t.z + o.z}; x.identity = false;
+        if (xf.simple && xf.flags == 0) {                  // the outermost wrapper: still [translation]
+          x.flags = INST_TRANSLATE; x.off[0] = h.u.translation.offset.x; x.off[1] = h.u.translation.offset.y; x.off[2] = h.u.translation.offset.z;
+        } else x.simple = false;
         flatten(h.u.translation.child, x, guard + 1);
       } break;
       case RT_OBJ_Y_ROTATION: {
         Xf x = xf; float c2 = h.u.y_rotation.cos_theta, s2 = h.u.y_rotation.sin_theta;
         x.c = xf.c * c2 - xf.s * s2; x.s = xf.s * c2 + xf.c * s2; x.identity = false;
+        if (xf.simple && !(xf.flags & INST_ROTATE)) { x.flags |= INST_ROTATE; x.sn = s2; x.cs = c2; }   // [translation] y-rotation
+        else x.simple = false;
         flatten(h.u.y_rotation.child, x, guard + 1);
       } break;
       case RT_OBJ_STRUCTURE:
@@ -469,6 +479,20 @@ struct Packer {
         break;
       default: break;
     }
+  }
+  // FAST traversal: a primitive under translation(y-rotation(.)), translation(.) or y-rotation(.) is NOT copied to world
+  // space: the leaf names an instance record (same layout as the fused instances of the reference-order walk) and the walk
+  // moves the ray into the primitive's space with the reference's own roundings, tests the reference's own record there and
+  // moves the hit back.  The reference's images carry the rounding behaviour of that arithmetic (a 10-unit sphere 1000 units
+  // from the camera is hit within ~0.02 units of its surface, inside or outside, and a bounce ray that starts inside hits the
+  // sphere again from within): world-space copies had other roundings and a measurably different picture of the 1000-sphere
+  // cluster of scene 3 (profiles/r2c_fast_bias_scene3.jsonl); this keeps the statistics.
+  uint32_t instanced_leaf(const Xf &xf, uint32_t child_tag) {
+    const uint32_t k = (uint32_t)(out.instances.size() / 2);
+    out.instances.push_back(f4(xf.off[0], xf.off[1], xf.off[2], as_float(child_tag)));
+    out.instances.push_back(f4(xf.sn, xf.cs, as_float(xf.flags), 0.0f));
+    ++out.instanced_leaves;
+    return make_ref(K_TRANSLATION, k);
   }
   void push_leaf(Leaf lf) {
     for (int a = 0; a < 3; ++a) lf.centroid[a] = 0.5f * (lf.box.lo[a] + lf.box.hi[a]);

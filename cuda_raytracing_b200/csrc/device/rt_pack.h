@@ -29,6 +29,7 @@ struct PackedScene {
   uint32_t ref_stack_need = 0, fast_stack_need = 0;
   uint32_t treelets = 0, treelet_prims = 0;   // own-BVH stand-ins inside the reference graph
   uint32_t fused_instances = 0;               // wrapper chains around one primitive / structure done as one item
+  uint32_t instanced_leaves = 0;              // FAST traversal: leaves of the own BVH tested in the primitive's own space
   uint32_t traversal_used = 0;           // RT_TRAVERSAL_REFERENCE or RT_TRAVERSAL_FAST
   std::map<uint64_t, uint32_t> checker_ids, noise_ids;   // arena offset -> table index (dedup)
   std::string error;

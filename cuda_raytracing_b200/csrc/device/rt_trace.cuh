@@ -591,6 +591,31 @@ __device__ __forceinline__ bool trace_flat(const Scene &sc, const Ray &r, float 
   return true;
 }
 
+// ---- instanced leaf of the own BVH (RT_TRAVERSAL_FAST on scenes with wrappers; rt_pack.cpp instanced_leaf) ----
+// the ray goes into the primitive's space with the reference's roundings (rt.cu:1176-1209), the hit comes back with them
+// (rt.cu:1210-1236, 1186-1188); `a` = d.d of the moved ray (a rotation changes its rounding)
+__device__ __forceinline__ void instance_enter(const float4 i0, const float4 i1, Ray &q, float &a) {
+  const uint32_t fl = __float_as_uint(i1.z);
+  if (fl & rtd::INST_TRANSLATE) q.o = vsub(q.o, v3(i0.x, i0.y, i0.z));
+  if (fl & rtd::INST_ROTATE) {
+    const float sn = i1.x, cs = i1.y;
+    const V3 o = q.o, d = q.d;
+    q.o = v3(ffma(o.x, cs, -fmul(o.z, sn)), o.y, ffma(o.x, sn, fmul(o.z, cs)));
+    q.d = v3(ffma(d.x, cs, -fmul(d.z, sn)), d.y, ffma(d.z, cs, fmul(d.x, sn)));
+    a = dot_xfirst(q.d, q.d);
+  }
+}
+__device__ __forceinline__ void instance_leave(const float4 i0, const float4 i1, Hit &h) {
+  const uint32_t fl = __float_as_uint(i1.z);
+  if (fl & rtd::INST_ROTATE) {
+    const float sn = i1.x, cs = i1.y;
+    const V3 p = h.p, n = h.n;
+    h.p = v3(ffma(p.x, cs, fmul(p.z, sn)), p.y, ffma(p.z, cs, -fmul(p.x, sn)));
+    h.n = v3(ffma(n.x, cs, fmul(n.z, sn)), n.y, ffma(n.z, cs, -fmul(n.x, sn)));
+  }
+  if (fl & rtd::INST_TRANSLATE) h.p = vadd(h.p, v3(i0.x, i0.y, i0.z));
+}
+
 // ================= own BVH (SAH, world-space primitives, near child first) =====================================
 // Closest hit is independent of visiting order and of (conservative) box culling, so for scenes without
 // instance wrappers this returns bit-identical hits to trace_reference at a fraction of the node visits.
@@ -638,13 +663,33 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
       cnt.planar();
       float tt;
       if (planar_t(sc, idx, kind == rtd::K_TRIANGLE, r, tmin, tmax, tt)) { tmax = tt; best = cur; }
+    } else if (kind == rtd::K_TRANSLATION) {              // instanced leaf: the primitive's own record, tested in its own space
+      const float4 i0 = ldg4(sc.instances + 2 * idx), i1 = ldg4(sc.instances + 2 * idx + 1);
+      Ray q = r;
+      float aq = a, tt;
+      instance_enter(i0, i1, q, aq);
+      const uint32_t child = __float_as_uint(i0.w), ck = rtd::ref_kind(child), ci = rtd::ref_index(child);
+      bool hit_in;
+      if (ck == rtd::K_SPHERE) { cnt.sphere(); hit_in = sphere_root(sc, ci, q, aq, tmin, tmax, tt); }
+      else { cnt.planar(); hit_in = planar_t(sc, ci, ck == rtd::K_TRIANGLE, q, tmin, tmax, tt); }
+      if (hit_in) { tmax = tt; best = cur; }
     }                                                     // K_NONE: the empty second child of a one-primitive scene
     if (sp == 0) break;
     cur = stk[(--sp) * stride];
   }
   if (best == 0xffffffffu) return false;
   if (rtd::ref_kind(best) == rtd::K_SPHERE) sphere_record(sc, rtd::ref_index(best), r, tmax, h);
-  else planar_record(sc, rtd::ref_index(best), r, tmax, h);
+  else if (rtd::ref_kind(best) == rtd::K_TRANSLATION) {
+    const uint32_t idx = rtd::ref_index(best);
+    const float4 i0 = ldg4(sc.instances + 2 * idx), i1 = ldg4(sc.instances + 2 * idx + 1);
+    Ray q = r;
+    float aq = a;
+    instance_enter(i0, i1, q, aq);
+    const uint32_t child = __float_as_uint(i0.w);
+    if (rtd::ref_kind(child) == rtd::K_SPHERE) sphere_record(sc, rtd::ref_index(child), q, tmax, h);
+    else planar_record(sc, rtd::ref_index(child), q, tmax, h);
+    instance_leave(i0, i1, h);
+  } else planar_record(sc, rtd::ref_index(best), r, tmax, h);
   return true;
 }
 

@@ -64,8 +64,11 @@ enum {
                                   conservative own walks keep (measured: 2 of 810 000 pixels on C2, 4 of 160 000 on C3
                                   through the BVH).  RT_TRAVERSAL_REFERENCE has neither. */
   RT_TRAVERSAL_REFERENCE = 1,  /* always walk the reference's own BVH in the reference's order */
-  RT_TRAVERSAL_FAST = 2        /* instances flattened to world space + SAH BVH: statistical (tier-2) parity only
-                                  when the scene has wrappers, identical to AUTO otherwise */
+  RT_TRAVERSAL_FAST = 2        /* one SAH BVH over world-space boxes of everything, instances included (an instanced
+                                  primitive is tested in its own space with the reference's arithmetic): statistical
+                                  (tier-2) parity only when the scene has wrappers -- the visiting order, and with it the
+                                  rounding drift the reference's wrappers leave on the ray, is not the reference's --
+                                  identical to AUTO otherwise */
 };
 int rt_scene_upload(rt_context *ctx, const rt_scene_desc *scene, uint32_t traversal);
 
@@ -187,6 +190,9 @@ typedef struct rt_pack_info {
   uint32_t perlin_tables, has_wrappers;
   uint32_t program_ops;                    /* ops of the linear program (0: none -- own BVH, too long, or odd wrapper nesting) */
   uint32_t program_boxes, program_prims, program_wrappers;   /* of which box tests, primitive tests, wrappers (ways in) */
+  uint32_t instanced_leaves;               /* RT_TRAVERSAL_FAST: leaves of the own BVH that are tested in the primitive's own space
+                                              (translation / y-rotation chains around one primitive): the reference's records and
+                                              the reference's arithmetic, so the rounding behaviour of its images is kept */
 } rt_pack_info;
 int rt_scene_pack_info(const rt_scene_desc *scene, uint32_t traversal, uint32_t treelet_min, uint32_t fuse_min, rt_pack_info *out);
 

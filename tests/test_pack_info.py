@@ -36,8 +36,10 @@ def test_final_scene_gets_treelets_and_fused_instances(product_lib):
     assert off.kernel_mode == 0 and off.treelets == 0 and off.fused_instances == 0 and off.own_nodes == 0
     small = hs.pack_info(treelet_min=2)                         # smaller subtrees qualify too: more treelets, more primitives
     assert small.treelets > i.treelets and small.treelet_prims > i.treelet_prims
-    fast = hs.pack_info(product_lib.RT_TRAVERSAL_FAST)          # instances flattened to world space: 1000 more sphere records
-    assert fast.spheres == 2005 and fast.own_nodes == 2401 + 5 + 1000 - 1   # one leaf per primitive in world space
+    fast = hs.pack_info(product_lib.RT_TRAVERSAL_FAST)          # one BVH over everything; the 1000 instanced spheres keep their own
+    assert fast.spheres == 1005 and fast.instanced_leaves == 1000          # records and are tested in their own space
+    assert fast.own_nodes == 2401 + 5 + 1000 - 1                # one leaf per primitive
+    assert i.instanced_leaves == 0
     hs.close()
 
 
