@@ -13,6 +13,7 @@
 // NCCL is bound at run time (dlopen of libnccl.so.2: the system library, or the one a host process such as PyTorch already
 // loaded), so the library itself has no link-time dependency on it and a single-GPU group needs no NCCL at all.
 #include <dlfcn.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <string>
@@ -36,6 +37,9 @@ struct NcclApi {
   const char *(*GetErrorString)(ncclResult_t) = nullptr;
   bool load(std::string &err) {
     if (handle) return true;
+    // NCCL prints its version / debug lines to stdout; the CLI's stdout is the reference's four lines (scripts scrape them):
+    // send NCCL's output to stderr unless the user chose a file
+    setenv("NCCL_DEBUG_FILE", "/dev/stderr", 0);
     handle = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
     if (!handle) handle = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
     if (!handle) { err = std::string("NCCL not found (dlopen libnccl.so.2): ") + dlerror(); return false; }
