@@ -146,9 +146,12 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
     // ---- claim work items for idle lanes: one atomic per warp ----
     // Lanes claim together, `claim_group` at a time (fewer only when the rest of the warp has nothing to do): items
     // claimed together are adjacent pixels, whose rays visit the same nodes (coherence), at the price of a short wait.
-    const bool want = (pix < 0) && !exhausted;
-    const unsigned m = __ballot_sync(full, want);
-    if (m && (__popc(m) >= a.claim_group || __popc(m) + __popc(__ballot_sync(full, exhausted)) == 32)) {
+    // One vote per iteration: which lanes hold a pixel.  `exhausted` is warp-uniform -- the queue is handed out in order,
+    // so once one claim of this warp came back past its end every later one would.
+    unsigned busy = __ballot_sync(full, pix >= 0);
+    const unsigned m = ~busy;
+    const bool want = pix < 0;
+    if (m && !exhausted && (__popc(m) >= a.claim_group || busy == 0u)) {
       const int leader = __ffs(m) - 1;
       unsigned long long first = 0;
       if ((int)lane == leader) first = atomicAdd(a.counters, (unsigned long long)__popc(m));
@@ -180,10 +183,10 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
             base = v3(fadd(ffma(fj, du.x, fmul(fi, dv.x)), a.p00[0]), fadd(ffma(fj, du.y, fmul(fi, dv.y)), a.p00[1]),
                       fadd(ffma(fj, du.z, fmul(fi, dv.z)), a.p00[2]));
           }
-        } else {
-          exhausted = true;
         }
       }
+      exhausted = first + (unsigned long long)__popc(m) > a.item_count;       // some claim of this round came back past the end
+      busy = __ballot_sync(full, pix >= 0);
     }
     // chunk k of a pixel starts from the state chunk k-1 left behind (ordered by the fence + progress counter).  The poll is
     // asynchronous: the value tested is the one requested an iteration ago, the next request goes out now and nobody reads
@@ -214,7 +217,10 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
         pix = -1;
       }
     }
-    if (!__any_sync(full, pix >= 0)) break;
+    if (busy == 0u) {                                     // nobody holds a pixel: done, or the slots claimed fell outside the image
+      if (exhausted) break;
+      continue;
+    }
     const bool live = pix >= 0 && !waiting;               // lanes without work stay in step (the warp shares work below)
 
     // ---- (1) camera ray generation (rt.cu:1570-1578) ----
