@@ -52,7 +52,7 @@ CONFIGS = {
 }
 KERNEL_MODES = {0: "reference order, stack walk", 1: "own SAH BVH", 2: "reference order + treelets + fused instances",
                 3: "reference order as a linear program (stackless)", 4: "linear program, short-lived pixels",
-                5: "tiny scene: every primitive, no BVH"}
+                5: "tiny scene: every primitive, no BVH", 6: "own SAH BVH with instanced leaves"}
 
 
 def host_threads():

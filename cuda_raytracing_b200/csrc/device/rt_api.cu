@@ -167,7 +167,7 @@ extern "C" {
 // 3 = reference order as a linear program (small scenes with wrappers), 2 = reference order with treelets / fused
 // instances, 0 = reference order through the stack
 static int kernel_mode(const rtp::PackedScene &p) {
-  if (p.traversal_used == RT_TRAVERSAL_FAST) return p.flat ? 5 : 1;
+  if (p.traversal_used == RT_TRAVERSAL_FAST) return p.flat ? 5 : (p.instanced_leaves > 0 ? 6 : 1);
   if (p.treelets + p.fused_instances > 0) return 2;
   return p.program.empty() ? 0 : 3;
 }
@@ -233,7 +233,7 @@ static void plan_render(int packed_mode, uint32_t traversal_used, uint32_t prims
   const long long life = (long long)spp * (long long)(bounces > 0 ? bounces : 1);       // bounces of a pixel's whole life, at most
   // short-lived pixels (the regime that gets no time slices either) on the stackless walk: the 5 x 96-register build
   if (mode == 3 && bounces <= 64 && life <= 256) mode = 4;
-  const double lanes = (double)sm_count * (mode == 3 ? 1024.0 : ((mode == 1 || mode == 5) ? 768.0 : 640.0));   // resident threads: 8, 6 or 5 blocks of 128 per SM
+  const double lanes = (double)sm_count * (mode == 3 ? 1024.0 : ((mode == 1 || mode == 5 || mode == 6) ? 768.0 : 640.0));   // resident threads: 8, 6 or 5 blocks of 128 per SM
   out->kernel_mode = (uint32_t)mode;
   out->resident_lanes = (uint32_t)lanes;
   // measured (profiles/r1_sweep_chunk_group.jsonl): big own-BVH scenes gain from claiming a whole warp of adjacent
@@ -271,7 +271,9 @@ static void plan_render(int packed_mode, uint32_t traversal_used, uint32_t prims
     return;
   }
   const double per_lane = (double)spp * (double)count / lanes;
-  int bulk = (int)(per_lane / 32.0);
+  // the tiny-scene walk (mode 5: the Perlin scenes) is bound by its slowest pixels' chains: fewer, longer chunks
+  // (scene 19 s512: 92 samples 66.2 ms, 128 63.1, 184 63.7; scene 17 in scattered order: 4 slices 22.9 ms, 2 slices 22.3)
+  int bulk = (int)(per_lane / (mode == 5 ? 24.0 : 32.0));
   // the 32-sample floor is the Cornell box's (cheap iterations, many of them); the hybrid walk over the big scene wants its
   // chunks short (scene 3 at s64: 13 samples 389 ms, 32 samples 409 ms), as before: never below 8
   const int floor_want = (mode == 3 || mode == 4) ? 32 : 8;
@@ -285,8 +287,8 @@ static void plan_render(int packed_mode, uint32_t traversal_used, uint32_t prims
   out->chunk_begin[0] = 0;
   if (bulk >= spp) {                                       // one chunk: nothing to slice
     out->chunk_begin[++n] = spp;
-  } else if (out->scattered && tiny_image && kn.scatter < 0) {   // tiny image in scattered order: 4 equal slices (see (a) above)
-    const int c = (spp + 3) / 4 > 8 ? (spp + 3) / 4 : 8;
+  } else if (out->scattered && tiny_image && kn.scatter < 0) {   // tiny image in scattered order: 2 equal slices (see (a) above)
+    const int c = (spp + 1) / 2 > 8 ? (spp + 1) / 2 : 8;
     while (done < spp) { done = done + c < spp ? done + c : spp; out->chunk_begin[++n] = done; }
   } else {
     if (kn.first_chunk > 0 && kn.first_chunk < bulk) { done = kn.first_chunk; out->chunk_begin[++n] = done; }   // RT_FIRST_CHUNK (experiments)
@@ -395,7 +397,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   a.count_rays = (p->flags & (RT_RENDER_COUNT_RAYS | RT_RENDER_COUNT_OPS)) ? 1u : 0u;
   a.count_ops = (p->flags & RT_RENDER_COUNT_OPS) ? 1u : 0u;
   a.forward = (p->flags & RT_RENDER_FORWARD_THROUGHPUT) ? 1u : 0u;
-  if (mode >= 3) a.stack_entries = 0;                      // neither the linear program nor the tiny-scene walk needs a traversal stack
+  if (mode >= 3 && mode <= 5) a.stack_entries = 0;         // neither the linear program nor the tiny-scene walk needs a traversal stack
   RT_CUDA(ctx, rtk::launch_render(a, mode, ctx->sm_count, s, &ctx->last_launch));
   ++launches;
   if (stats) {

@@ -51,7 +51,7 @@ constexpr int RT_MIN_BLOCKS_FAST = 6, RT_MIN_BLOCKS_REF = 5;
 #ifndef RT_MIN_BLOCKS_LINEAR
 #define RT_MIN_BLOCKS_LINEAR 8
 #endif
-constexpr int min_blocks(int mode) { return (mode == 1 || mode == 5) ? RT_MIN_BLOCKS_FAST : (mode == 3 ? RT_MIN_BLOCKS_LINEAR : RT_MIN_BLOCKS_REF); }
+constexpr int min_blocks(int mode) { return (mode == 1 || mode == 5 || mode == 6) ? RT_MIN_BLOCKS_FAST : (mode == 3 ? RT_MIN_BLOCKS_LINEAR : RT_MIN_BLOCKS_REF); }
 
 __device__ __forceinline__ void stage_perlin(const Scene &sc, PerlinSmem *dst) {
   for (int i = threadIdx.x; i < 256; i += blockDim.x) {
@@ -75,8 +75,9 @@ __device__ __forceinline__ bool trace(const Scene &sc, Ray &r, Hit &h, uint32_t 
   if (MODE == 0) return rtt::trace_reference<false>(sc, r, 0.001f, inf, h, stk, stride, cnt);
   if (MODE == 2) return rtt::trace_reference<true>(sc, r, 0.001f, inf, h, stk, stride, cnt);   // reference order + treelets
   if (MODE == 5) return rtt::trace_flat(sc, r, 0.001f, inf, h, cnt);                            // tiny scene: every primitive
+  if (MODE == 6) return rtt::trace_fast<true>(sc, r, 0.001f, inf, h, stk, stride, cnt);         // own BVH with instanced leaves
   if (MODE >= 3) return rtt::trace_linear(sc, r, 0.001f, inf, h, cnt);                          // reference order, stackless
-  return rtt::trace_fast(sc, r, 0.001f, inf, h, stk, stride, cnt);
+  return rtt::trace_fast<false>(sc, r, 0.001f, inf, h, stk, stride, cnt);
 }
 
 // rendered set -> image: the set is a run of rows, or interleaved bands of rows (tile sharding in one launch)
@@ -465,7 +466,8 @@ __global__ void __launch_bounds__(PROBE_BLOCK) probe_trace_kernel(const Scene sc
   if (MODE == 0) hit = rtt::trace_reference<true>(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
   else if (MODE == 3) hit = rtt::trace_linear(sc, r, tmin, tmax, h, cnt);
   else if (MODE == 5) hit = rtt::trace_flat(sc, r, tmin, tmax, h, cnt);
-  else hit = rtt::trace_fast(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
+  else if (MODE == 6) hit = rtt::trace_fast<true>(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
+  else hit = rtt::trace_fast<false>(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
   rt_probe_hit o;
   o.origin[0] = r.o.x; o.origin[1] = r.o.y; o.origin[2] = r.o.z;
   o.direction[0] = r.d.x; o.direction[1] = r.d.y; o.direction[2] = r.d.z;
@@ -516,6 +518,7 @@ cudaError_t launch_probe_trace(const rtd::Scene &scene, int mode, uint64_t n, co
   if (mode == 0) probe_trace_kernel<0><<<probe_grid(n), PROBE_BLOCK, smem, stream>>>(scene, n, origins, directions, times, tmin, tmax, out);
   else if (mode == 3) probe_trace_kernel<3><<<probe_grid(n), PROBE_BLOCK, 0, stream>>>(scene, n, origins, directions, times, tmin, tmax, out);
   else if (mode == 5) probe_trace_kernel<5><<<probe_grid(n), PROBE_BLOCK, 0, stream>>>(scene, n, origins, directions, times, tmin, tmax, out);
+  else if (mode == 6) probe_trace_kernel<6><<<probe_grid(n), PROBE_BLOCK, smem, stream>>>(scene, n, origins, directions, times, tmin, tmax, out);
   else probe_trace_kernel<1><<<probe_grid(n), PROBE_BLOCK, smem, stream>>>(scene, n, origins, directions, times, tmin, tmax, out);
   return cudaGetLastError();
 }
@@ -585,6 +588,7 @@ cudaError_t launch_render(const rtd::RenderArgs &args, int mode, int sm_count, c
     if (mode == 0) return launch_render_t<0, 256, true>(args, sm_count, stream, info);
     if (mode == 2) return launch_render_t<2, 256, true>(args, sm_count, stream, info);
     if (mode == 5) return launch_render_t<5, 256, true>(args, sm_count, stream, info);
+    if (mode == 6) return launch_render_t<6, 256, true>(args, sm_count, stream, info);
     if (mode >= 3) return launch_render_t<3, 256, true>(args, sm_count, stream, info);
     return launch_render_t<1, 256, true>(args, sm_count, stream, info);
   }
@@ -592,6 +596,7 @@ cudaError_t launch_render(const rtd::RenderArgs &args, int mode, int sm_count, c
     if (mode == 0) return launch_render_t<0, 0, false>(args, sm_count, stream, info);
     if (mode == 2) return launch_render_t<2, 0, false>(args, sm_count, stream, info);
     if (mode == 5) return launch_render_t<5, 0, false>(args, sm_count, stream, info);
+    if (mode == 6) return launch_render_t<6, 0, false>(args, sm_count, stream, info);
     if (mode == 4) return launch_render_t<4, 0, false>(args, sm_count, stream, info);
     if (mode == 3) return launch_render_t<3, 0, false>(args, sm_count, stream, info);
     return launch_render_t<1, 0, false>(args, sm_count, stream, info);
@@ -599,6 +604,7 @@ cudaError_t launch_render(const rtd::RenderArgs &args, int mode, int sm_count, c
   if (mode == 0) return small ? launch_render_t<0, 64, false>(args, sm_count, stream, info) : launch_render_t<0, 256, false>(args, sm_count, stream, info);
   if (mode == 2) return small ? launch_render_t<2, 64, false>(args, sm_count, stream, info) : launch_render_t<2, 256, false>(args, sm_count, stream, info);
   if (mode == 5) return small ? launch_render_t<5, 64, false>(args, sm_count, stream, info) : launch_render_t<5, 256, false>(args, sm_count, stream, info);
+  if (mode == 6) return small ? launch_render_t<6, 64, false>(args, sm_count, stream, info) : launch_render_t<6, 256, false>(args, sm_count, stream, info);
   if (mode == 4 && small) return launch_render_t<4, 64, false>(args, sm_count, stream, info);   // mode 3 at 5 x 96 registers
   if (mode >= 3) return small ? launch_render_t<3, 64, false>(args, sm_count, stream, info) : launch_render_t<3, 256, false>(args, sm_count, stream, info);
   return small ? launch_render_t<1, 64, false>(args, sm_count, stream, info) : launch_render_t<1, 256, false>(args, sm_count, stream, info);

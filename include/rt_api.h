@@ -182,7 +182,8 @@ int rt_probe_xorwow(rt_context *ctx, uint64_t seed, uint64_t first_subsequence, 
 typedef struct rt_pack_info {
   uint32_t traversal_used;                 /* RT_TRAVERSAL_REFERENCE or RT_TRAVERSAL_FAST */
   uint32_t kernel_mode;                    /* 0 reference order, 1 own BVH, 2 reference order + treelets / fused instances,
-                                              3 reference order as a linear program walked by whole warps */
+                                              3 reference order as a stackless linear program, 5 tiny scene: every primitive,
+                                              6 own BVH with instanced leaves (RT_TRAVERSAL_FAST on a scene with wrappers) */
   uint32_t spheres, planars;               /* primitive records (flattened instances included in FAST mode) */
   uint32_t own_nodes;                      /* 64-byte own-BVH nodes (whole scene, or all treelets) */
   uint32_t treelets, treelet_prims, fused_instances;

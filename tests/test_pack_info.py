@@ -11,8 +11,9 @@ def test_every_scene_packs_in_every_mode(product_lib, sid):
         assert 1 <= i.stack_need <= i.stack_capacity
         assert i.spheres + i.planars >= 1
         tiny = not i.has_wrappers and i.spheres <= 4 and i.planars <= 4       # walked without its BVH (kernel mode 5)
-        if trav == product_lib.RT_TRAVERSAL_FAST:
-            assert (i.traversal_used, i.kernel_mode) == (product_lib.RT_TRAVERSAL_FAST, 5 if tiny else 1) and i.own_nodes >= 1
+        if trav == product_lib.RT_TRAVERSAL_FAST:           # one own BVH; instanced leaves where the scene has wrappers (kernel mode 6)
+            assert (i.traversal_used, i.kernel_mode) == (product_lib.RT_TRAVERSAL_FAST, 5 if tiny else (6 if i.instanced_leaves else 1)) and i.own_nodes >= 1
+            assert (i.instanced_leaves > 0) == bool(i.has_wrappers)
         if trav == product_lib.RT_TRAVERSAL_REFERENCE:          # the literal walk: no stand-ins
             assert (i.traversal_used, i.kernel_mode) == (product_lib.RT_TRAVERSAL_REFERENCE, 0)
             assert i.treelets == i.fused_instances == i.own_nodes == 0

@@ -33,7 +33,7 @@ def test_plans_of_the_baseline_configs(product_lib):
         got[name] = (pl.kernel_mode, pl.resident_lanes, list(pl.chunk_begin)[:pl.chunk_count + 1], pl.claim_group, pl.scattered)
     assert got["C1"] == (4, 148 * 640, [0, 16], 1, 0)                        # short-lived pixels: 5 x 96 build, one chunk
     assert got["C2"] == (1, 148 * 768, [0, 57, 114, 171, 214, 235, 246, 256], 32, 0)
-    assert got["C3"] == (5, 148 * 768, [0, 128, 256, 384, 512], 1, 1)        # tiny image: 4 equal slices, scattered order
+    assert got["C3"] == (5, 148 * 768, [0, 256, 512], 1, 1)                  # tiny image: 2 equal slices, scattered order
     assert got["C4"][:2] == (3, 148 * 1024) and got["C4"][2][:13] == [76 * k for k in range(13)]   # 12 equal chunks of 1/32 of a lane's share ...
     assert got["C4"][2][13:] == [968, 996, 1010, 1024]                       # ... then a halving tail
     assert got["C4/8"] == (3, 148 * 1024, [0, 32, 64, 96, 112, 120, 128], 1, 0)   # an 8-GPU share of C4: never below 32 samples in the bulk
