@@ -126,6 +126,7 @@ struct RenderArgs {
   uint32_t count_rays;
   uint32_t count_ops;            // run the instrumented kernel variant (per-ray operation counts for F_ray)
   uint32_t forward;              // RT_RENDER_FORWARD_THROUGHPUT: attenuation product carried forwards in registers
+  uint32_t linear_smem_word;     // kernel modes 3 / 4: word offset of the staged program / records inside dynamic shared memory
 };
 
 constexpr int STACK_CAPACITY = 32;     // traversal stack entries per thread (shared memory, [slot][thread])

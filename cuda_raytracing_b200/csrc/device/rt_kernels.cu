@@ -69,6 +69,18 @@ __device__ __forceinline__ void count_values(const rtt::OpCount &c, unsigned lon
 __device__ __forceinline__ uint32_t ld_volatile_u32(const uint32_t *p) { return *reinterpret_cast<const volatile uint32_t *>(p); }
 __device__ __forceinline__ void st_volatile_u32(uint32_t *p, uint32_t v) { *reinterpret_cast<volatile uint32_t *>(p) = v; }
 
+#ifndef RT_LINEAR_SMEM
+#define RT_LINEAR_SMEM 1
+#endif
+// kernel modes 3 / 4 with RT_LINEAR_SMEM: the linear program, the planar and the sphere records of the (small) scene are
+// staged in shared memory when they fit, and the walk reads them with generic loads (measured, r2i_linear_program_in_smem.jsonl:
+// Cornell box s1024 309.6 -> 306.1 ms, s128 42.6 -> 41.6 ms, scene 0 1.100 -> 1.071 ms; RT_LINEAR_SMEM=0 builds the global-memory walk)
+constexpr uint32_t LINEAR_SMEM_MAX_BYTES = 16384;
+__host__ __device__ inline uint32_t linear_smem_bytes(const Scene &sc) {
+  const uint32_t b = 32u * sc.program_ops + 64u * sc.planar_count + 32u * sc.sphere_count;
+  return (RT_LINEAR_SMEM && sc.program_ops > 0 && b <= LINEAR_SMEM_MAX_BYTES) ? b : 0u;
+}
+
 template <int MODE, class C>
 __device__ __forceinline__ bool trace(const Scene &sc, Ray &r, Hit &h, uint32_t *stk, int stride, C &cnt) {
   const float inf = __uint_as_float(0x7f800000u);
@@ -76,7 +88,8 @@ __device__ __forceinline__ bool trace(const Scene &sc, Ray &r, Hit &h, uint32_t 
   if (MODE == 2) return rtt::trace_reference<true>(sc, r, 0.001f, inf, h, stk, stride, cnt);   // reference order + treelets
   if (MODE == 5) return rtt::trace_flat(sc, r, 0.001f, inf, h, cnt);                            // tiny scene: every primitive
   if (MODE == 6) return rtt::trace_fast<true>(sc, r, 0.001f, inf, h, stk, stride, cnt);         // own BVH with instanced leaves
-  if (MODE >= 3) return rtt::trace_linear(sc, r, 0.001f, inf, h, cnt);                          // reference order, stackless
+  if (MODE >= 3) return RT_LINEAR_SMEM ? rtt::trace_linear<true>(sc, r, 0.001f, inf, h, cnt)    // reference order, stackless
+                                        : rtt::trace_linear<false>(sc, r, 0.001f, inf, h, cnt);
   return rtt::trace_fast<false>(sc, r, 0.001f, inf, h, stk, stride, cnt);
 }
 
@@ -95,7 +108,20 @@ __device__ __forceinline__ size_t image_pixel(const RenderArgs &a, int pix) {
 template <int MODE, int MAXB, bool COUNT>
 __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(const RenderArgs a) {
   extern __shared__ __align__(16) uint32_t smem[];
+#if RT_LINEAR_SMEM
+  Scene sc = a.scene;
+  if ((MODE == 3 || MODE == 4) && linear_smem_bytes(a.scene) > 0) {         // block-uniform; the staging area is the last part of smem
+    float4 *dst = reinterpret_cast<float4 *>(smem + a.linear_smem_word);
+    const uint32_t n_prog = 2u * sc.program_ops, n_plan = 4u * sc.planar_count, n_sph = 2u * sc.sphere_count;
+    for (uint32_t i = threadIdx.x; i < n_prog; i += blockDim.x) dst[i] = __ldg(a.scene.program + i);
+    for (uint32_t i = threadIdx.x; i < n_plan; i += blockDim.x) dst[n_prog + i] = __ldg(a.scene.planars + i);
+    for (uint32_t i = threadIdx.x; i < n_sph; i += blockDim.x) dst[n_prog + n_plan + i] = __ldg(a.scene.spheres + i);
+    sc.program = dst; sc.planars = dst + n_prog; sc.spheres = dst + n_prog + n_plan;
+    __syncthreads();
+  }
+#else
   const Scene &sc = a.scene;
+#endif
   uint32_t *stk = smem + threadIdx.x;
   constexpr int stride = RT_BLOCK;                       // launch_render_t always launches RT_BLOCK threads
   PerlinSmem *perlin = nullptr;
@@ -123,7 +149,9 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
   float att_r[FWD ? 1 : MAXB], att_g[FWD ? 1 : MAXB], att_b[FWD ? 1 : MAXB];
   V3 thr = v3(1.0f, 1.0f, 1.0f);
   // noise-textured bounces park {point, scale} in their slot; evaluated when (and if) the path has something to unwind
-  constexpr bool DEFER = !FWD && (RT_NOISE_AT_PATH_END != 0);
+  // (not in the stackless walk of the small scenes, modes 3 / 4: none of them has a noise texture and its 320 bytes per
+  // thread would only widen a local-memory frame that already spills past L2 -- such a scene evaluates per bounce)
+  constexpr bool DEFER = !FWD && (RT_NOISE_AT_PATH_END != 0) && MODE != 3 && MODE != 4;
   float att_s[DEFER ? MAXB : 1];
   uint8_t nslot[DEFER ? MAXB : 1];                       // the parked slots of the current path, in order
   int n_noise = 0;
@@ -545,6 +573,12 @@ template <int MODE, int MAXB, bool COUNT>
 static cudaError_t launch_render_t(const RenderArgs &args, int sm_count, cudaStream_t stream, LaunchInfo *info) {
   size_t smem = sizeof(uint32_t) * (size_t)args.stack_entries * RT_BLOCK;
   if (args.scene.perlin_tables > 0) smem += sizeof(PerlinSmem) + sizeof(float) * rts::SCRATCH_WORDS_PER_WARP * (RT_BLOCK / 32);
+  RenderArgs largs = args;
+  if (MODE == 3 || MODE == 4) {
+    smem = (smem + 15) & ~size_t(15);
+    largs.linear_smem_word = (uint32_t)(smem / 4);
+    smem += linear_smem_bytes(args.scene);
+  }
   auto kernel = render_kernel<MODE, MAXB, COUNT>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
@@ -578,7 +612,7 @@ static cudaError_t launch_render_t(const RenderArgs &args, int sm_count, cudaStr
     cudaFuncGetAttributes(&fa, kernel);
     info->grid = (int)grid; info->block = RT_BLOCK; info->regs = fa.numRegs; info->blocks_per_sm = per_sm; info->smem = smem;
   }
-  kernel<<<(unsigned)grid, RT_BLOCK, smem, stream>>>(args);
+  kernel<<<(unsigned)grid, RT_BLOCK, smem, stream>>>(largs);
   return cudaGetLastError();
 }
 

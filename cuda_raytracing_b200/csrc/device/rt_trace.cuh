@@ -34,6 +34,9 @@ struct Hit {
 };
 
 __device__ __forceinline__ float4 ldg4(const float4 *p) { return __ldg(p); }
+// G = the record may have been staged in shared memory (kernel modes 3 / 4 with RT_LINEAR_SMEM): a generic load finds it
+// wherever it is; everything else reads global memory through the read-only path
+template <bool G> __device__ __forceinline__ float4 ldx(const float4 *p) { return G ? *p : __ldg(p); }
 
 // Per-ray operation counters for the roofline's F_ray; NoCount compiles to nothing.
 struct NoCount {
@@ -55,10 +58,11 @@ struct OpCount {
 // ---- sphere (rt.cu:1093-1123): a = d.d is passed in (it only changes when a wrapper rotates the ray) ----
 // The test (which root, if any, lies in (tmin,tmax)) and the hit record are separate so that the warp-scheduled
 // kernel can carry only (t, prim) through a traversal and build the record once, for the closest hit.
+template <bool G = false>
 __device__ __forceinline__ bool sphere_root(const Scene &sc, uint32_t idx, const Ray &r, float a, float tmin, float tmax,
                                             float &root_out) {
-  const float4 s0 = ldg4(sc.spheres + 2 * idx);
-  const float4 s1 = ldg4(sc.spheres + 2 * idx + 1);
+  const float4 s0 = ldx<G>(sc.spheres + 2 * idx);
+  const float4 s1 = ldx<G>(sc.spheres + 2 * idx + 1);
   const V3 c = v3(ffma(r.time, s1.x, s0.x), ffma(r.time, s1.y, s0.y), ffma(r.time, s1.z, s0.z));   // movement_path_at
   const V3 oc = vsub(c, r.o);
   const float b = fmul(dot_yfirst(r.d, oc), -2.0f);
@@ -73,9 +77,10 @@ __device__ __forceinline__ bool sphere_root(const Scene &sc, uint32_t idx, const
   root_out = root;
   return true;
 }
+template <bool G = false>
 __device__ __forceinline__ void sphere_record(const Scene &sc, uint32_t idx, const Ray &r, float root, Hit &h) {
-  const float4 s0 = ldg4(sc.spheres + 2 * idx);
-  const float4 s1 = ldg4(sc.spheres + 2 * idx + 1);
+  const float4 s0 = ldx<G>(sc.spheres + 2 * idx);
+  const float4 s1 = ldx<G>(sc.spheres + 2 * idx + 1);
   const V3 c = v3(ffma(r.time, s1.x, s0.x), ffma(r.time, s1.y, s0.y), ffma(r.time, s1.z, s0.z));
   h.t = root;
   h.p = along(r.o, root, r.d);
@@ -93,11 +98,12 @@ __device__ __forceinline__ void sphere_record(const Scene &sc, uint32_t idx, con
   h.n = h.front ? n : vneg(n);
   h.prim = idx;
 }
+template <bool G = false>
 __device__ __forceinline__ bool hit_sphere(const Scene &sc, uint32_t idx, const Ray &r, float a, float tmin, float &tmax,
                                            Hit &h) {
   float root;
-  if (!sphere_root(sc, idx, r, a, tmin, tmax, root)) return false;
-  sphere_record(sc, idx, r, root, h);
+  if (!sphere_root<G>(sc, idx, r, a, tmin, tmax, root)) return false;
+  sphere_record<G>(sc, idx, r, root, h);
   tmax = root;
   return true;
 }
@@ -118,15 +124,16 @@ __device__ __forceinline__ bool planar_inside_rec(const float4 p1, const float4 
   if (triangle) inside = inside && (fadd(alpha, beta) <= 1.0f);
   return inside;
 }
+template <bool G = false>
 __device__ __forceinline__ bool planar_inside(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float t, V3 &p,
                                               float &alpha, float &beta) {
-  const float4 p1 = ldg4(sc.planars + 4 * idx + 1);        // q, w.x
-  const float4 p2 = ldg4(sc.planars + 4 * idx + 2);        // v, w.y
-  const float4 p3 = ldg4(sc.planars + 4 * idx + 3);        // u, w.z
+  const float4 p1 = ldx<G>(sc.planars + 4 * idx + 1);      // q, w.x
+  const float4 p2 = ldx<G>(sc.planars + 4 * idx + 2);      // v, w.y
+  const float4 p3 = ldx<G>(sc.planars + 4 * idx + 3);      // u, w.z
   return planar_inside_rec(p1, p2, p3, triangle, r, t, p, alpha, beta);
 }
 // `p0` = first word of the record (normal, d): the linear program carries it inside the op, the other walks load it here
-template <bool EAGER = false>
+template <bool EAGER = false, bool G = false>
 __device__ __forceinline__ bool planar_t_p0(const Scene &sc, const float4 p0, uint32_t idx, bool triangle, const Ray &r, float tmin,
                                             float tmax, float &t_out) {
   float4 p1 = p0, p2 = p0, p3 = p0;
@@ -145,7 +152,7 @@ __device__ __forceinline__ bool planar_t_p0(const Scene &sc, const float4 p0, ui
   const float t = zero_num ? __uint_as_float((__float_as_uint(num) ^ __float_as_uint(denom)) & 0x80000000u) : quot;
   if (!(tmin <= t && t <= tmax)) return false;
   V3 p; float alpha, beta;
-  if (EAGER ? !planar_inside_rec(p1, p2, p3, triangle, r, t, p, alpha, beta) : !planar_inside(sc, idx, triangle, r, t, p, alpha, beta)) return false;
+  if (EAGER ? !planar_inside_rec(p1, p2, p3, triangle, r, t, p, alpha, beta) : !planar_inside<G>(sc, idx, triangle, r, t, p, alpha, beta)) return false;
   t_out = t;
   return true;
 }
@@ -154,11 +161,12 @@ __device__ __forceinline__ bool planar_t(const Scene &sc, uint32_t idx, bool tri
                                          float &t_out) {
   return planar_t_p0<EAGER>(sc, ldg4(sc.planars + 4 * idx), idx, triangle, r, tmin, tmax, t_out);
 }
+template <bool G = false>
 __device__ __forceinline__ void planar_record_p0(const Scene &sc, const float4 p0, uint32_t idx, const Ray &r, float t, Hit &h) {
   const V3 n = v3(p0.x, p0.y, p0.z);
   const float denom = dot_yfirst(n, r.d);
   float alpha, beta;
-  planar_inside(sc, idx, false, r, t, h.p, alpha, beta);
+  planar_inside<G>(sc, idx, false, r, t, h.p, alpha, beta);
   h.u = alpha; h.v = beta; h.t = t;
   h.front = denom < 0.0f;
   h.n = h.front ? n : vneg(n);
@@ -176,12 +184,12 @@ __device__ __forceinline__ bool hit_planar(const Scene &sc, uint32_t idx, bool t
   tmax = t;
   return true;
 }
-template <bool EAGER = false>
+template <bool EAGER = false, bool G = false>
 __device__ __forceinline__ bool hit_planar_p0(const Scene &sc, const float4 p0, uint32_t idx, bool triangle, const Ray &r, float tmin,
                                               float &tmax, Hit &h) {
   float t;
-  if (!planar_t_p0<EAGER>(sc, p0, idx, triangle, r, tmin, tmax, t)) return false;
-  planar_record_p0(sc, p0, idx, r, t, h);
+  if (!planar_t_p0<EAGER, G>(sc, p0, idx, triangle, r, tmin, tmax, t)) return false;
+  planar_record_p0<G>(sc, p0, idx, r, t, h);
   tmax = t;
   return true;
 }
@@ -438,7 +446,7 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
 // issued once per warp and ray) ran 14 % SLOWER than the stack walk: 7 % fewer warp-instructions, but every step a
 // serial chain vote -> op load -> branch -> test, and the lanes' inside tests no longer overlap across quads.
 constexpr uint32_t OP_T_EXIT = 6u, OP_R_EXIT = 7u, OP_IN_WRAPPER = 0x100u;
-template <class C>
+template <bool G = false, class C>
 __device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin, float tmax, Hit &h, C &cnt) {
   bool result = false, was_last_hit = false;
   V3 inv = v3(frcp(r.d.x), frcp(r.d.y), frcp(r.d.z));
@@ -458,19 +466,19 @@ __device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin
       nx0 = ldg4(sc.program + 2 * nx); nx1 = ldg4(sc.program + 2 * nx + 1);
     }
 #else
-    const float4 w0 = ldg4(sc.program + 2 * pc), w1 = ldg4(sc.program + 2 * pc + 1);
+    const float4 w0 = ldx<G>(sc.program + 2 * pc), w1 = ldx<G>(sc.program + 2 * pc + 1);
 #endif
     const uint32_t code = __float_as_uint(w1.w), arg = __float_as_uint(w1.z);
     ++pc;
     switch (code & 7u) {
       case rtd::K_SPHERE:
         cnt.sphere();
-        if (hit_sphere(sc, arg, r, a, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
+        if (hit_sphere<G>(sc, arg, r, a, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
         break;
       case rtd::K_TRIANGLE:
       case rtd::K_QUAD:
         cnt.planar();
-        if (hit_planar_p0(sc, w0, arg, (code & 7u) == rtd::K_TRIANGLE, r, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
+        if (hit_planar_p0<false, G>(sc, w0, arg, (code & 7u) == rtd::K_TRIANGLE, r, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
         break;
       case rtd::K_BVH: {
         float t0 = tmin, t1 = tmax;
