@@ -171,6 +171,10 @@ def lib():
         L.rt_mat_lambert_image_pixels.restype = Material
         L.rt_add_sphere.argtypes = [C.POINTER(World), Xform, Vec3, C.c_float, Material]
         L.rt_add_sphere.restype = C.c_uint32
+        L.rt_add_quad.argtypes = [C.POINTER(World), Xform, Vec3, Vec3, Vec3, Material]
+        L.rt_add_quad.restype = C.c_uint32
+        L.rt_mat_metal.argtypes = [Vec3, C.c_float]
+        L.rt_mat_metal.restype = Material
         L.rt_world_stack_bound.argtypes = [C.POINTER(World)]
         L.rt_world_stack_bound.restype = C.c_uint64
         L.rt_default_render_settings.argtypes = [C.POINTER(RenderSettings)]
@@ -224,6 +228,10 @@ class HostScene:
 
     def add_sphere(self, center, radius, material):
         return lib().rt_add_sphere(C.byref(self.world), Xform(), Vec3(*[float(x) for x in center]), float(radius), material)
+
+    def add_quad(self, q, u, v, material):
+        vec = lambda a: Vec3(*[float(x) for x in a])
+        return lib().rt_add_quad(C.byref(self.world), Xform(), vec(q), vec(u), vec(v), material)
 
     def build_bvh(self):
         return lib().rt_world_build_bvh(C.byref(self.world))

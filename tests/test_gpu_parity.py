@@ -695,3 +695,53 @@ def test_fast_traversal_geometry_vs_oracle(gpu_ctx, oracle, product_lib, sid):
     print("fast-vs-oracle geometry, scene %d: %d rays, %d differ: %s" % (sid, len(O), len(bad), bad[:6]))
     assert len(bad) <= len(O) // 500, (sid, len(bad))           # grazing rays / ties may fall either way
     hs.close()
+
+
+@pytest.mark.gpu
+def test_coplanar_quads_tie_is_the_documented_difference(gpu_ctx, oracle, product_lib):
+    """rt_api.h, RT_TRAVERSAL_AUTO: on a scene without wrappers the own BVH returns the reference's closest hit except for
+    candidates at exactly the same t.  Two coplanar, overlapping quads of different materials (lambertian over metal):
+    RT_TRAVERSAL_REFERENCE returns the oracle's hit bit for bit (the reference's inclusive planar test lets the quad it
+    visits last win); RT_TRAVERSAL_AUTO returns the same t / point / normal and may name the other quad."""
+    hs = product_lib.HostScene(None)
+    lam = hs.mat_lambert_solid((0.2, 0.7, 0.2))
+    met = product_lib.lib().rt_mat_metal(product_lib.api.Vec3(0.8, 0.8, 0.8), 0.0)
+    hs.add_quad((-1, -1, -2), (2, 0, 0), (0, 2, 0), lam)
+    hs.add_quad((-0.5, -0.5, -2), (2, 0, 0), (0, 2, 0), met)          # same plane z = -2, overlapping the first
+    hs.add_sphere((0, -101.5, -2), 100.0, hs.mat_lambert_solid((0.5, 0.5, 0.5)))
+    hs.build_bvh()
+    sc = common.oracle_scene(oracle, hs)
+    L = oracle.lib()
+    L.orc_set_fma_profile(1)
+    rng = np.random.default_rng(11)
+    n = 3000
+    o = np.zeros((n, 3), np.float32)
+    d = np.stack([rng.uniform(-0.9, 1.4, n), rng.uniform(-0.9, 1.4, n), np.full(n, -2.0)], axis=1).astype(np.float32)
+    t = np.zeros(n, np.float32)
+    try:
+        gpu_ctx.upload(hs, product_lib.RT_TRAVERSAL_REFERENCE)
+        ref = gpu_ctx.probe_trace(o, d, t)
+        gpu_ctx.upload(hs, product_lib.RT_TRAVERSAL_AUTO)
+        own = gpu_ctx.probe_trace(o, d, t)
+        both = other = 0
+        for i in range(n):
+            oo, dd = o[i].copy(), d[i].copy()
+            rec = oracle.OrcHit()
+            h = L.orc_hit(C.byref(sc.c), oracle.fptr(oo), oracle.fptr(dd), 0.0, 0.001, float("inf"), C.byref(rec))
+            assert ref[i].hit == h and own[i].hit == h
+            if not h:
+                continue
+            assert common.bits(np.float32(ref[i].t)) == common.bits(np.float32(rec.t)) and ref[i].material_type == rec.mat[0]
+            assert common.bits(np.float32(own[i].t)) == common.bits(np.float32(rec.t))
+            assert list(own[i].point[:]) == list(rec.point[:]) and list(own[i].normal[:]) == list(rec.normal[:])
+            inside_both = -0.5 <= d[i, 0] <= 1.0 and -0.5 <= d[i, 1] <= 1.0
+            if inside_both:
+                both += 1
+                other += own[i].material_type != rec.mat[0]
+            else:
+                assert own[i].material_type == rec.mat[0]
+        print("coplanar quads: %d rays in the overlap, the own BVH names the other quad on %d" % (both, other))
+        assert both > 300
+    finally:
+        L.orc_set_fma_profile(0)
+    hs.close()
