@@ -6,4 +6,4 @@ api.py (ctypes mirror).  The CUDA library is the product; importing this package
 from .api import (Context, Group, HostScene, RtError, lib, LIB_PATH, EXPORTS, write_ppm,  # noqa: F401
                   RT_TRAVERSAL_AUTO, RT_TRAVERSAL_REFERENCE, RT_TRAVERSAL_FAST,
                   RT_RENDER_OUTPUT_SUM, RT_RENDER_NO_RNG_CACHE, RT_RENDER_COUNT_RAYS, RT_RENDER_COUNT_OPS, RT_RENDER_RESUME,
-                  RT_RENDER_FORWARD_THROUGHPUT, RT_SHARD_TILES, RT_SHARD_SAMPLES, OP_NAMES)
+                  RT_RENDER_FORWARD_THROUGHPUT, RT_STATIC_SCRATCH_MAX_PIXELS, RT_SHARD_TILES, RT_SHARD_SAMPLES, OP_NAMES)

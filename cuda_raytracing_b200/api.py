@@ -14,6 +14,7 @@ LIB_PATH = os.environ.get("RT_B200_LIB") or os.path.join(_HERE, "libraytracing_b
 RT_TRAVERSAL_AUTO, RT_TRAVERSAL_REFERENCE, RT_TRAVERSAL_FAST = 0, 1, 2
 RT_RENDER_OUTPUT_SUM, RT_RENDER_NO_RNG_CACHE, RT_RENDER_COUNT_RAYS, RT_RENDER_COUNT_OPS, RT_RENDER_RESUME = 1, 2, 4, 8, 16
 RT_RENDER_FORWARD_THROUGHPUT = 32
+RT_STATIC_SCRATCH_MAX_PIXELS = 262144
 RT_SHARD_TILES, RT_SHARD_SAMPLES = 0, 1
 OP_NAMES = ["box", "sphere", "planar", "translation", "rotation", "lambert", "metal", "glass", "light", "noise", "checker", "arena"]
 
@@ -100,7 +101,7 @@ class ProbeHit(C.Structure):  # rt_probe_hit
 EXPORTS = [
     # rt_api.h
     "rt_context_create", "rt_context_destroy", "rt_last_error_string", "rt_context_set_stream", "rt_context_reset_stream", "rt_scene_upload",
-    "rt_render_params_from_camera", "rt_render_device", "rt_resolve_device", "rt_render", "rt_synchronize",
+    "rt_render_params_from_camera", "rt_render_device", "rt_render_device_static", "rt_resolve_device", "rt_render", "rt_synchronize",
     "rt_render_state_save", "rt_render_state_load",
     "rt_group_create", "rt_group_destroy", "rt_group_size", "rt_group_context", "rt_group_last_error", "rt_group_render_world",
     "rt_scene_pack_info", "rt_render_plan_query", "rt_scene_program", "rt_render_world", "rt_probe_trace", "rt_probe_scatter", "rt_probe_texture", "rt_probe_xorwow",
@@ -135,6 +136,7 @@ def lib():
         L.rt_render_params_from_camera.argtypes = [C.POINTER(RenderSettings), C.POINTER(Camera), C.POINTER(RenderParams)]
         L.rt_render_params_from_camera.restype = None
         L.rt_render_device.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.POINTER(Stats)]
+        L.rt_render_device_static.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p]
         L.rt_resolve_device.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_float, C.c_void_p]
         L.rt_render.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_void_p, C.POINTER(Stats)]
         L.rt_synchronize.argtypes = [C.c_void_p]
@@ -356,6 +358,11 @@ class Context:
         _check(lib().rt_render_device(self._h, C.byref(params), C.c_void_p(device_ptr), C.byref(st) if stats else None),
                self._h)
         return st
+
+    def render_device_static(self, params, device_ptr):
+        """rt_render_device without any allocation: the kernel's scratch is the library's static device array
+        (at most RT_STATIC_SCRATCH_MAX_PIXELS pixels per call; calls on one GPU must not overlap)."""
+        _check(lib().rt_render_device_static(self._h, C.byref(params), C.c_void_p(device_ptr)), self._h)
 
     def resolve_device(self, pixels_ptr, n_pixels, scale, rgb8_ptr):
         _check(lib().rt_resolve_device(self._h, C.c_void_p(pixels_ptr), n_pixels, scale, C.c_void_p(rgb8_ptr)), self._h)

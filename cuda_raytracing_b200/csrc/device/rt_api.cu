@@ -9,6 +9,7 @@
 #include <algorithm>
 
 #include <chrono>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -626,3 +627,116 @@ int rt_probe_xorwow(rt_context *ctx, uint64_t seed, uint64_t first_subsequence, 
 }
 
 }  // extern "C"
+
+// ---- rt_render_device_static: the render without any allocation ---------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops).  The render kernel's scratch -- the work-claim / statistics counters, the
+// per-pixel chunk progress and the per-pixel XORWOW states it parks between chunks -- lives in ONE file-scope device array
+// of fixed size instead of the context's grown buffers.  Every device that loads the library holds the array until exit
+// (7 MiB); every call on a device shares it, so two calls that overlap on one GPU race.
+namespace {
+constexpr uint32_t kStaticMaxPixels = RT_STATIC_SCRATCH_MAX_PIXELS;
+constexpr size_t kStaticCounterWords = 64;                                     // 16 u64 counters, padded to 256 B
+constexpr size_t kStaticWords = kStaticCounterWords + 7 * (size_t)kStaticMaxPixels;   // + progress (1) + XORWOW state (6) per pixel
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mutex;
+uint32_t *g_static_ptr[kStaticMaxDevices] = {};      // the array's DEVICE address on each device, resolved once per device
+}  // namespace
+static __device__ __align__(256) uint32_t g_static_scratch[kStaticWords];
+
+// In host code `g_static_scratch` is a host-side stand-in for the symbol, not a device address: the address a kernel can use
+// comes from cudaGetSymbolAddress, asked once per device with that device current.
+static int static_scratch_address(rt_context *ctx, uint32_t **out) {
+  if (ctx->device < 0 || ctx->device >= kStaticMaxDevices) return fail(ctx, RT_ERR_UNSUPPORTED, "rt_render_device_static: device index beyond 63");
+  std::lock_guard<std::mutex> lock(g_static_mutex);
+  if (!g_static_ptr[ctx->device]) {
+    void *ptr = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&ptr, g_static_scratch);        // the caller made ctx->device current
+    if (e != cudaSuccess || !ptr) return cuda_fail(ctx, e, "rt_render_device_static: cudaGetSymbolAddress(static scratch)");
+    g_static_ptr[ctx->device] = (uint32_t *)ptr;
+  }
+  *out = g_static_ptr[ctx->device];
+  return RT_OK;
+}
+
+extern "C" int rt_render_device_static(rt_context *ctx, const rt_render_params *p, float *d_pixels) {
+  int row0, row1;
+  int rc = check_params(ctx, p, &row0, &row1);
+  if (rc != RT_OK) return rc;
+  if (!d_pixels) return fail(ctx, RT_ERR_INVALID, "rt_render_device_static: d_pixels_rgb is NULL");
+  if (p->flags & RT_RENDER_RESUME)
+    return fail(ctx, RT_ERR_INVALID, "rt_render_device_static: RT_RENDER_RESUME is not supported (the shared scratch does not keep a render's states)");
+  RenderSet set;
+  rc = render_set(ctx, p, row0, row1, &set);
+  if (rc != RT_OK) return rc;
+  if (set.rows == 0) return RT_OK;                         // more ranks than bands: nothing to do for this one
+  if (set.count > kStaticMaxPixels)
+    return fail(ctx, RT_ERR_UNSUPPORTED, "rt_render_device_static: the call renders " + std::to_string(set.count) + " pixels, the static scratch holds " +
+                                             std::to_string(kStaticMaxPixels) + " (RT_STATIC_SCRATCH_MAX_PIXELS); use rt_render_device or render by rows");
+  RT_CUDA(ctx, cudaSetDevice(ctx->device));
+  uint32_t *scratch = nullptr;
+  rc = static_scratch_address(ctx, &scratch);
+  if (rc != RT_OK) return rc;
+  unsigned long long *counters = (unsigned long long *)scratch;
+  uint32_t *progress = scratch + kStaticCounterWords;
+  uint32_t *states = progress + kStaticMaxPixels;
+  cudaStream_t s = ctx->stream;
+  const uint64_t count = set.count;
+
+  // XORWOW states straight into the scratch (no cache of pristine states: that would be a second array)
+  if (!set.banded) {
+    RT_CUDA(ctx, rtk::launch_rng_init(p->seed, set.first_sub, count, (const uint32_t *)ctx->b_rng_mats.ptr, states, s));
+  } else {
+    uint64_t done = 0;
+    for (uint64_t b = p->band_phase; b * p->band_rows < (uint64_t)p->img_height; b += p->band_period) {
+      const uint64_t lo = b * p->band_rows, hi = lo + p->band_rows;
+      const uint64_t n = ((hi < (uint64_t)p->img_height ? hi : (uint64_t)p->img_height) - lo) * p->img_width;
+      RT_CUDA(ctx, rtk::launch_rng_init(p->seed, lo * p->img_width + p->subsequence_offset, n, (const uint32_t *)ctx->b_rng_mats.ptr, states + 6 * done, s));
+      done += n;
+    }
+  }
+  // the array keeps the last call's contents: the claim counter and the chunk progress must start at zero
+  RT_CUDA(ctx, cudaMemsetAsync(progress, 0, count * sizeof(uint32_t), s));
+  RT_CUDA(ctx, cudaMemsetAsync(counters, 0, 16 * sizeof(unsigned long long), s));
+
+  rtd::RenderArgs a;
+  memset(&a, 0, sizeof(a));
+  a.scene = ctx->scene;
+  a.pixels = d_pixels;
+  a.rng_states = states;
+  a.progress = progress;
+  a.counters = counters;
+  const int bounces = p->max_bounces & 255;
+  PlanKnobs knobs;
+  knobs.chunk_samples = ctx->chunk_samples; knobs.claim_group = ctx->claim_group; knobs.scatter = ctx->scatter; knobs.tile_w = ctx->tile_w;
+  knobs.first_chunk = ctx->first_chunk;
+  rt_render_plan plan;
+  plan_render(kernel_mode(ctx->packed), ctx->packed.traversal_used, ctx->packed.sphere_count + ctx->packed.planar_count, p->img_width, set.rows,
+              p->samples_per_pixel, bounces, ctx->sm_count, knobs, &plan);
+  const int mode = (int)plan.kernel_mode;
+  a.chunk_samples = plan.chunk_samples;
+  a.chunk_count = (int32_t)plan.chunk_count;
+  for (int k = 0; k <= rtd::MAX_CHUNK_TABLE; ++k) a.chunk_begin[k] = plan.chunk_begin[k];
+  a.claim_group = (int32_t)plan.claim_group;
+  const uint32_t tw = (uint32_t)ctx->tile_w, th = 32u / tw;
+  while ((1u << a.tile_shift) < tw) ++a.tile_shift;
+  a.first_row = row0;
+  if (set.banded) { a.band_rows = (int32_t)p->band_rows; a.band_period = (int32_t)p->band_period; a.band_phase = (int32_t)p->band_phase; }
+  a.tiles_x = ((uint32_t)p->img_width + tw - 1) / tw;
+  a.slots_per_chunk = a.tiles_x * ((set.rows + th - 1) / th) * 32u;
+  a.item_count = (unsigned long long)a.slots_per_chunk * (unsigned long long)a.chunk_count;
+  if (plan.scattered) a.scatter_mul = scatter_multiplier(a.slots_per_chunk);
+  a.stack_entries = (mode >= 3 && mode <= 5) ? 0 : (int32_t)ctx->scene.stack_entries;
+  a.img_width = p->img_width; a.img_height = p->img_height;
+  a.samples_per_pixel = p->samples_per_pixel; a.max_bounces = bounces;
+  a.first_pixel = (int32_t)set.first_pixel; a.pixel_count = (int32_t)count;
+  a.defocus_angle = p->defocus_angle;
+  memcpy(a.background, p->background, 12); memcpy(a.dv, p->pixel_delta_v, 12); memcpy(a.du, p->pixel_delta_u, 12);
+  memcpy(a.cam, p->camera_pos, 12); memcpy(a.ddu, p->defocus_disk_u, 12); memcpy(a.ddv, p->defocus_disk_v, 12);
+  memcpy(a.p00, p->pixel00, 12);
+  a.sample_scale = (p->flags & RT_RENDER_OUTPUT_SUM) ? 1.0f : 1.0f / (float)p->samples_per_pixel;
+  a.forward = (p->flags & RT_RENDER_FORWARD_THROUGHPUT) ? 1u : 0u;
+  rtk::LaunchInfo info;                                    // not kept: the context's record belongs to rt_render_device
+  RT_CUDA(ctx, rtk::launch_render(a, mode, ctx->sm_count, s, &info));
+  return RT_OK;
+}

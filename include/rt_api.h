@@ -126,6 +126,20 @@ void rt_render_params_from_camera(const rt_render_settings *s, const rt_camera *
  * tensor); rows outside [row_begin,row_end) are left untouched.  Asynchronous on the context's stream except
  * for stats (stats != NULL synchronises). */
 int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels_rgb, rt_stats *stats);
+/* rt_render_device WITHOUT any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same kernels, same image bit for bit as rt_render_device; the render kernel's scratch (claim counters, per-pixel chunk
+ * progress, per-pixel XORWOW states: 28 B per pixel) lives in one file-scope `static __device__` array of
+ * 256 + 28 * RT_STATIC_SCRATCH_MAX_PIXELS bytes (7 MiB) that every GPU loading the library holds until exit.  The call makes
+ * no cudaMalloc / cudaFree and no allocating library call; it only enqueues on the context's stream (the first call on a
+ * device also resolves the array's device address with cudaGetSymbolAddress: make it outside a capture).
+ * Limits: the rendered set (rows x img_width, or the rows of the bands) must not exceed RT_STATIC_SCRATCH_MAX_PIXELS
+ * -> RT_ERR_UNSUPPORTED with the two numbers in the message (render by rows instead); no RT_RENDER_RESUME, no stats.
+ * Every call on a device SHARES the array: it clears what must start at zero itself, but two calls whose kernels overlap on
+ * one GPU (two contexts / streams on the same device) race -- serialise them.  The scene upload and rt_context_create
+ * before it do allocate; d_pixels_rgb is the caller's buffer as in rt_render_device. */
+#define RT_STATIC_SCRATCH_MAX_PIXELS 262144u               /* 512 x 512 */
+int rt_render_device_static(rt_context *ctx, const rt_render_params *p, float *d_pixels_rgb);
 /* gamma + clamp + 8-bit quantise on the device (rt.cu:1391-1433): rgb8 = (u8)(256*clamp(sqrt(scale*x),0,0.999)) */
 int rt_resolve_device(rt_context *ctx, const float *d_pixels_rgb, uint64_t n_pixels, float scale, uint8_t *d_rgb8);
 /* host buffers: renders, resolves and copies back (h_rgb8 and/or h_pixels_rgb may be NULL) */
