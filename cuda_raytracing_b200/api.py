@@ -83,7 +83,7 @@ class PackInfo(C.Structure):  # rt_pack_info
     _fields_ = [(n, C.c_uint32) for n in ("traversal_used", "kernel_mode", "spheres", "planars", "own_nodes", "treelets",
                                           "treelet_prims", "fused_instances", "stack_need", "stack_capacity", "perlin_tables",
                                           "has_wrappers", "program_ops", "program_boxes", "program_prims",
-                                          "program_wrappers", "instanced_leaves")]
+                                          "program_wrappers", "instanced_leaves", "program_axis_quads")]
 
 
 class RenderPlan(C.Structure):  # rt_render_plan

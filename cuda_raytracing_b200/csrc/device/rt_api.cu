@@ -71,6 +71,7 @@ int rt_context_create(int device_id, rt_context **out) {
   if (const char *v = getenv("RT_LINEAR")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->linear = (int)x; }
   if (const char *v = getenv("RT_FLAT")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->flat = (int)x; }
   if (const char *v = getenv("RT_SCATTER")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->scatter = (int)x; }
+  if (const char *v = getenv("RT_AXIS_QUADS")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= 1) ctx->axis_quads = (int)x; }
   if (const char *v = getenv("RT_FIRST_CHUNK")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 24)) ctx->first_chunk = (int)x; }
   if (const char *v = getenv("RT_CLAIM_GROUP")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= 32) ctx->claim_group = (int)x; }
   std::vector<uint32_t> mats;
@@ -88,7 +89,7 @@ void rt_context_destroy(rt_context *ctx) {
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   DeviceBuffer *all[] = {&ctx->b_ref_nodes, &ctx->b_xforms, &ctx->b_instances, &ctx->b_structs, &ctx->b_struct_children, &ctx->b_fast_nodes,
-                         &ctx->b_spheres, &ctx->b_planars, &ctx->b_materials, &ctx->b_checkers, &ctx->b_perlin_vec,
+                         &ctx->b_spheres, &ctx->b_planars, &ctx->b_planars_axis, &ctx->b_materials, &ctx->b_checkers, &ctx->b_perlin_vec,
                          &ctx->b_perlin_perm, &ctx->b_arena, &ctx->b_program, &ctx->b_rng_mats, &ctx->b_rng_init, &ctx->b_rng_states,
                          &ctx->b_progress, &ctx->b_counters,
                          &ctx->b_pixels, &ctx->b_rgb8};
@@ -139,7 +140,7 @@ int rtc::upload_packed(rt_context *ctx, const rtp::PackedScene &packed) {
   UP(b_ref_nodes, p.ref_nodes); UP(b_xforms, p.xforms); UP(b_instances, p.instances); UP(b_structs, p.structures); UP(b_struct_children, p.struct_children);
   UP(b_fast_nodes, p.fast_nodes); UP(b_spheres, p.spheres); UP(b_planars, p.planars); UP(b_materials, p.materials);
   UP(b_checkers, p.checkers); UP(b_perlin_vec, p.perlin_vectors); UP(b_perlin_perm, p.perlin_perm); UP(b_arena, p.tex_arena);
-  UP(b_program, p.program);
+  UP(b_program, p.program); UP(b_planars_axis, p.planars_axis);
 #undef UP
   RT_CUDA(ctx, cudaStreamSynchronize(s));       // the host vectors may be reused after return
   rtd::Scene &sc = ctx->scene;
@@ -149,6 +150,7 @@ int rtc::upload_packed(rt_context *ctx, const rtp::PackedScene &packed) {
   sc.program = (const float4 *)ctx->b_program.ptr; sc.program_ops = (uint32_t)(p.program.size() / 2);
   sc.ref_root = p.ref_root; sc.fast_nodes = (const float4 *)ctx->b_fast_nodes.ptr; sc.fast_root = p.fast_root;
   sc.spheres = (const float4 *)ctx->b_spheres.ptr; sc.planars = (const float4 *)ctx->b_planars.ptr;
+  sc.planars_axis = (p.program_axis_quads && ctx->axis_quads != 0) ? (const float4 *)ctx->b_planars_axis.ptr : nullptr;
   sc.sphere_count = p.sphere_count; sc.planar_count = p.planar_count; sc.flat_triangles = p.flat_triangles;
   sc.materials = (const uint4 *)ctx->b_materials.ptr; sc.checkers = (const float4 *)ctx->b_checkers.ptr;
   sc.perlin_vectors = (const float4 *)ctx->b_perlin_vec.ptr; sc.perlin_perm = (const uint8_t *)ctx->b_perlin_perm.ptr;
@@ -598,6 +600,7 @@ int rt_scene_pack_info(const rt_scene_desc *scene, uint32_t traversal, uint32_t 
   out->stack_capacity = (uint32_t)rtd::STACK_CAPACITY;
   out->perlin_tables = p.perlin_tables; out->has_wrappers = p.has_wrappers ? 1u : 0u;
   out->instanced_leaves = p.instanced_leaves;
+  out->program_axis_quads = p.program_axis_quads ? 1u : 0u;
   return RT_OK;
 }
 

@@ -49,12 +49,13 @@ struct rt_context {
   bool has_scene = false;
   rtd::Scene scene{};
   rtp::PackedScene packed;
-  rtc::DeviceBuffer b_ref_nodes, b_xforms, b_instances, b_structs, b_struct_children, b_fast_nodes, b_spheres, b_planars, b_materials,
+  rtc::DeviceBuffer b_ref_nodes, b_xforms, b_instances, b_structs, b_struct_children, b_fast_nodes, b_spheres, b_planars, b_planars_axis, b_materials,
       b_checkers, b_perlin_vec, b_perlin_perm, b_arena, b_program;
   // rng
   rtc::DeviceBuffer b_rng_mats, b_rng_init, b_rng_states, b_progress, b_counters;   // b_rng_init: pristine states (cache)
   int chunk_samples = 0;                                   // 0 = automatic; env RT_CHUNK overrides (tuning knob)
   int claim_group = 0;                                     // 0 = automatic; env RT_CLAIM_GROUP (tuning knob)
+  int axis_quads = 1;                                      // env RT_AXIS_QUADS=0: keep the general inside test for axis-aligned quads (bisecting)
   int first_chunk = 0;                                     // env RT_FIRST_CHUNK: a short first chunk in front of the schedule (experiments)
   uint32_t fuse_min = 8;                                   // env RT_FUSE_MIN: wrapper chains around one object become one item when there are this many (0 = never)
   uint32_t treelet_min = 8;                                // env RT_TREELET_MIN: smallest wrapper-free subtree given an own BVH (0 = none)

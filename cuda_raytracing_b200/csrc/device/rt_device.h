@@ -83,6 +83,9 @@ struct Scene {
   // primitives
   const float4 *spheres;        // 2 per sphere: {cx,cy,cz,r} {mx,my,mz, flags (bit0: needs uv)}
   const float4 *planars;        // 4 per quad/triangle: {n.xyz,d} {q.xyz,w.x} {v.xyz,w.y} {u.xyz,w.z}
+  // linear program whose planar ops are all axis-aligned quads: {n.xyz,d} {q.xyz,w.k} {S_alpha.xyz,0} {S_beta.xyz,0}
+  // (rt_pack.cpp axis_aligned_words; read by the axis variant of trace_linear only), nullptr otherwise
+  const float4 *planars_axis;
   uint32_t sphere_count, planar_count;
   uint32_t flat_triangles;      // trace_flat (tiny scenes, kernel mode 5): bit i set = planar i is a triangle
   // second primitive set for flattened instances (FAST mode on scenes with wrappers) lives in the same arrays

@@ -81,15 +81,15 @@ __host__ __device__ inline uint32_t linear_smem_bytes(const Scene &sc) {
   return (RT_LINEAR_SMEM && sc.program_ops > 0 && b <= LINEAR_SMEM_MAX_BYTES) ? b : 0u;
 }
 
-template <int MODE, class C>
+template <int MODE, bool AX, class C>
 __device__ __forceinline__ bool trace(const Scene &sc, Ray &r, Hit &h, uint32_t *stk, int stride, C &cnt) {
   const float inf = __uint_as_float(0x7f800000u);
   if (MODE == 0) return rtt::trace_reference<false>(sc, r, 0.001f, inf, h, stk, stride, cnt);
   if (MODE == 2) return rtt::trace_reference<true>(sc, r, 0.001f, inf, h, stk, stride, cnt);   // reference order + treelets
   if (MODE == 5) return rtt::trace_flat(sc, r, 0.001f, inf, h, cnt);                            // tiny scene: every primitive
   if (MODE == 6) return rtt::trace_fast<true>(sc, r, 0.001f, inf, h, stk, stride, cnt);         // own BVH with instanced leaves
-  if (MODE >= 3) return RT_LINEAR_SMEM ? rtt::trace_linear<true>(sc, r, 0.001f, inf, h, cnt)    // reference order, stackless
-                                        : rtt::trace_linear<false>(sc, r, 0.001f, inf, h, cnt);
+  if (MODE >= 3) return RT_LINEAR_SMEM ? rtt::trace_linear<true, AX>(sc, r, 0.001f, inf, h, cnt)    // reference order, stackless
+                                        : rtt::trace_linear<false, AX>(sc, r, 0.001f, inf, h, cnt);
   return rtt::trace_fast<false>(sc, r, 0.001f, inf, h, stk, stride, cnt);
 }
 
@@ -105,22 +105,26 @@ __device__ __forceinline__ size_t image_pixel(const RenderArgs &a, int pix) {
   return (size_t)image_row(a, y) * (size_t)a.img_width + (size_t)(pix - y * a.img_width);
 }
 
-template <int MODE, int MAXB, bool COUNT>
+// AX (kernel modes 3 / 4 only): every planar op of the program is an axis-aligned quad; the walk reads Scene::planars_axis
+// and runs the reduced inside test (planar_inside_axis in rt_trace.cuh) -- same roundings, fewer instructions, no triangle case
+template <int MODE, int MAXB, bool COUNT, bool AX = false>
 __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(const RenderArgs a) {
   extern __shared__ __align__(16) uint32_t smem[];
 #if RT_LINEAR_SMEM
   Scene sc = a.scene;
+  if (AX) sc.planars = a.scene.planars_axis;
   if ((MODE == 3 || MODE == 4) && linear_smem_bytes(a.scene) > 0) {         // block-uniform; the staging area is the last part of smem
     float4 *dst = reinterpret_cast<float4 *>(smem + a.linear_smem_word);
     const uint32_t n_prog = 2u * sc.program_ops, n_plan = 4u * sc.planar_count, n_sph = 2u * sc.sphere_count;
     for (uint32_t i = threadIdx.x; i < n_prog; i += blockDim.x) dst[i] = __ldg(a.scene.program + i);
-    for (uint32_t i = threadIdx.x; i < n_plan; i += blockDim.x) dst[n_prog + i] = __ldg(a.scene.planars + i);
+    for (uint32_t i = threadIdx.x; i < n_plan; i += blockDim.x) dst[n_prog + i] = __ldg((AX ? a.scene.planars_axis : a.scene.planars) + i);
     for (uint32_t i = threadIdx.x; i < n_sph; i += blockDim.x) dst[n_prog + n_plan + i] = __ldg(a.scene.spheres + i);
     sc.program = dst; sc.planars = dst + n_prog; sc.spheres = dst + n_prog + n_plan;
     __syncthreads();
   }
 #else
-  const Scene &sc = a.scene;
+  Scene sc = a.scene;
+  if (AX) sc.planars = a.scene.planars_axis;
 #endif
   uint32_t *stk = smem + threadIdx.x;
   constexpr int stride = RT_BLOCK;                       // launch_render_t always launches RT_BLOCK threads
@@ -279,7 +283,7 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
     if (live && !done) {
       ++rays;
       Hit h; h.u = 0.0f; h.v = 0.0f; h.t = 0.0f; h.prim = 0; h.front = 0; h.p = cam; h.n = cam;
-      if (trace<MODE>(sc, ray, h, stk, stride, cnt)) {
+      if (trace<MODE, AX>(sc, ray, h, stk, stride, cnt)) {
         const uint4 m0 = __ldg(sc.materials + 2 * h.prim);
         if (COUNT) {
           const uint32_t ty = m0.x & 0xffu, tk = (m0.x >> 8) & 0xffu;
@@ -492,7 +496,14 @@ __global__ void __launch_bounds__(PROBE_BLOCK) probe_trace_kernel(const Scene sc
   bool hit;
   rtt::NoCount cnt;
   if (MODE == 0) hit = rtt::trace_reference<true>(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
-  else if (MODE == 3) hit = rtt::trace_linear(sc, r, tmin, tmax, h, cnt);
+  else if (MODE == 3) {
+    if (sc.planars_axis != nullptr) {                      // the walk the render kernel runs on this scene (AX)
+      Scene ax = sc; ax.planars = sc.planars_axis;
+      hit = rtt::trace_linear<false, true>(ax, r, tmin, tmax, h, cnt);
+    } else {
+      hit = rtt::trace_linear(sc, r, tmin, tmax, h, cnt);
+    }
+  }
   else if (MODE == 5) hit = rtt::trace_flat(sc, r, tmin, tmax, h, cnt);
   else if (MODE == 6) hit = rtt::trace_fast<true>(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
   else hit = rtt::trace_fast<false>(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
@@ -569,7 +580,7 @@ cudaError_t launch_probe_texture(const rtd::Scene &scene, uint64_t n, uint32_t t
 // launch_render: persistent grid = SMs x resident blocks per SM (occupancy API), so every SM is full and the
 // work queue does the load balancing.
 // ======================================================================================================
-template <int MODE, int MAXB, bool COUNT>
+template <int MODE, int MAXB, bool COUNT, bool AX = false>
 static cudaError_t launch_render_t(const RenderArgs &args, int sm_count, cudaStream_t stream, LaunchInfo *info) {
   size_t smem = sizeof(uint32_t) * (size_t)args.stack_entries * RT_BLOCK;
   if (args.scene.perlin_tables > 0) smem += sizeof(PerlinSmem) + sizeof(float) * rts::SCRATCH_WORDS_PER_WARP * (RT_BLOCK / 32);
@@ -579,7 +590,7 @@ static cudaError_t launch_render_t(const RenderArgs &args, int sm_count, cudaStr
     largs.linear_smem_word = (uint32_t)(smem / 4);
     smem += linear_smem_bytes(args.scene);
   }
-  auto kernel = render_kernel<MODE, MAXB, COUNT>;
+  auto kernel = render_kernel<MODE, MAXB, COUNT, AX>;
   cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   // shared memory carve-out: what the resident blocks need (the scene data and the attenuation stacks live in L1, so
@@ -625,6 +636,11 @@ cudaError_t launch_render(const rtd::RenderArgs &args, int mode, int sm_count, c
     if (mode == 6) return launch_render_t<6, 256, true>(args, sm_count, stream, info);
     if (mode >= 3) return launch_render_t<3, 256, true>(args, sm_count, stream, info);
     return launch_render_t<1, 256, true>(args, sm_count, stream, info);
+  }
+  if (args.scene.planars_axis != nullptr && (mode == 3 || mode == 4)) {   // linear program of axis-aligned quads (see render_kernel, AX)
+    if (args.forward) return mode == 4 ? launch_render_t<4, 0, false, true>(args, sm_count, stream, info) : launch_render_t<3, 0, false, true>(args, sm_count, stream, info);
+    if (mode == 4 && small) return launch_render_t<4, 64, false, true>(args, sm_count, stream, info);
+    return small ? launch_render_t<3, 64, false, true>(args, sm_count, stream, info) : launch_render_t<3, 256, false, true>(args, sm_count, stream, info);
   }
   if (args.forward) {                                    // RT_RENDER_FORWARD_THROUGHPUT: no attenuation stack (MAXB = 0)
     if (mode == 0) return launch_render_t<0, 0, false>(args, sm_count, stream, info);

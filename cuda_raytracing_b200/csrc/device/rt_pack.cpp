@@ -6,6 +6,7 @@
 #include "rt_pack.h"
 
 #include <math.h>
+#include <cmath>
 #include <string.h>
 
 #include <algorithm>
@@ -351,6 +352,58 @@ struct Packer {
     }
     return found;
   }
+  // ---- axis-aligned quads of a linear program: the inside test in reduced form (planar_inside_axis in rt_trace.cuh) ----
+  // alpha = dot(w, cross(p - q, v)), beta = dot(w, cross(u, p - q)) (rt.cu:1069-1070).  When w, u and v each have exactly one
+  // non-zero component (w along axis k, u and v along the two others), every other term of the two cross products and of the
+  // dot product is a product with an exact zero: the reference's fma chains then reduce, rounding for rounding, to
+  //   alpha = fl(w.k * fl((p - q).m * s)),   with {m, s} = {a, v.b} or {b, -v.a}  ((k, a, b) cyclic),
+  //   beta  = fl(w.k * fl((p - q).m' * s')), with {m', s'} = {b, u.a} or {a, -u.b}
+  // (only the sign of an exact zero result can differ, which no comparison and no texture lookup sees).  The record keeps
+  // the scale as a vector S with s at position m and zeros elsewhere, so the kernel needs no indexing: fl(pl.m * s) is
+  // dot(pl, S) evaluated as the usual fma chain.  Words: {n, d} {q, w.k} {S_alpha, 0} {S_beta, 0}.
+  static int single_axis(const rt_vec3 &a) {
+    const float c[3] = {a.x, a.y, a.z};
+    int k = -1;
+    for (int i = 0; i < 3; ++i) {
+      if (c[i] != c[i] || std::isinf(c[i])) return -1;
+      if (c[i] != 0.0f) { if (k >= 0) return -1; k = i; }
+    }
+    return k;
+  }
+  void axis_aligned_words() {
+    const size_t n_planar = out.planars.size() / 4;
+    std::vector<uint8_t> seen(n_planar, 0);
+    std::vector<float4> words(out.planars);
+    size_t quads = 0;
+    for (size_t op = 0; op + 1 < out.program.size(); op += 2) {
+      uint32_t code, arg;
+      memcpy(&code, &out.program[op + 1].w, 4); memcpy(&arg, &out.program[op + 1].z, 4);
+      if ((code & 7u) == K_TRIANGLE) return;
+      if ((code & 7u) != K_QUAD) continue;
+      if (arg >= n_planar) return;
+      ++quads;
+      if (seen[arg]) continue;
+      seen[arg] = 1;
+      const float4 p0 = out.planars[4 * arg], p1 = out.planars[4 * arg + 1], p2 = out.planars[4 * arg + 2], p3 = out.planars[4 * arg + 3];
+      const rt_vec3 nrm = {p0.x, p0.y, p0.z}, w = {p1.w, p2.w, p3.w}, v = {p2.x, p2.y, p2.z}, u = {p3.x, p3.y, p3.z};
+      const int k = single_axis(w), kn = single_axis(nrm), jv = single_axis(v), iu = single_axis(u);
+      if (k < 0 || kn != k || jv < 0 || iu < 0 || jv == k || iu == k || jv == iu) return;
+      if (!std::isfinite(p1.x) || !std::isfinite(p1.y) || !std::isfinite(p1.z) || !std::isfinite(p0.w)) return;
+      const int a = (k + 1) % 3, b = (k + 2) % 3;
+      const float vc[3] = {v.x, v.y, v.z}, uc[3] = {u.x, u.y, u.z}, wc[3] = {w.x, w.y, w.z};
+      float sa[3] = {0.0f, 0.0f, 0.0f}, sb[3] = {0.0f, 0.0f, 0.0f};
+      // cross(pl, v).k = fma(pl.a, v.b, -(pl.b * v.a));  cross(u, pl).k = fma(u.a, pl.b, -(u.b * pl.a))
+      if (jv == b) sa[a] = vc[b]; else sa[b] = -vc[a];
+      if (iu == a) sb[b] = uc[a]; else sb[a] = -uc[b];
+      words[4 * arg + 1] = f4(p1.x, p1.y, p1.z, wc[k]);
+      words[4 * arg + 2] = f4(sa[0], sa[1], sa[2], 0.0f);
+      words[4 * arg + 3] = f4(sb[0], sb[1], sb[2], 0.0f);
+    }
+    if (quads == 0) return;
+    out.planars_axis.swap(words);
+    out.program_axis_quads = true;
+  }
+
   // ---- the reference-order walk as a linear program (trace_linear in rt_trace.cuh) ----
   // Static replay of the stack machine of trace_reference with every box entered: a BVH node pushes right then left (left
   // is walked first; a leaf node with left == right tests its object twice, as the reference does), a structure pushes
@@ -573,6 +626,8 @@ struct Packer {
         !emit_program(root_href, false, false, 0)) {
       out.program.clear(); out.program_boxes = out.program_prims = out.program_wrappers = 0;
     }
+
+    if (!out.program.empty()) axis_aligned_words();
 
     // own BVH over the whole scene
     if (want_fast) {

@@ -16,6 +16,10 @@ struct PackedScene {
   std::vector<float4> ref_nodes, xforms, instances, fast_nodes, spheres, planars, checkers, perlin_vectors;
   std::vector<float4> program;           // reference-order walk as a linear program (2 per op), empty when not available
   uint32_t program_boxes = 0, program_prims = 0, program_wrappers = 0;   // op counts by kind (wrappers: ways in)
+  // every planar op of the program is a QUAD whose normal / u / v / w each have ONE non-zero component (walls, boxes):
+  // planars_axis holds its inside test in reduced form, 4 words per planar like `planars` (see rt_pack.cpp axis_aligned_words)
+  std::vector<float4> planars_axis;
+  bool program_axis_quads = false;
   std::vector<uint2> structures;
   std::vector<uint32_t> struct_children;
   std::vector<uint4> materials;          // 2 per primitive id

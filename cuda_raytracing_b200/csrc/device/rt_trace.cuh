@@ -132,8 +132,23 @@ __device__ __forceinline__ bool planar_inside(const Scene &sc, uint32_t idx, boo
   const float4 p3 = ldx<G>(sc.planars + 4 * idx + 3);      // u, w.z
   return planar_inside_rec(p1, p2, p3, triangle, r, t, p, alpha, beta);
 }
+// Axis-aligned quad (Scene::planars_axis, words {q, w.k} {S_alpha} {S_beta}; rt_pack.cpp axis_aligned_words has the
+// derivation): with one non-zero component in each of w, u, v the reference's two cross products and dot products reduce,
+// rounding for rounding, to alpha = fl(w.k * fl(pl.m * s)) -- fl(pl.m * s) evaluated as dot(pl, S), S zero except s at m,
+// so that no component has to be picked at run time.  18 instead of 30 operations for the two coordinates.
+template <bool G = false>
+__device__ __forceinline__ bool planar_inside_axis(const Scene &sc, uint32_t idx, const Ray &r, float t, V3 &p, float &alpha, float &beta) {
+  const float4 p1 = ldx<G>(sc.planars + 4 * idx + 1);      // q, w.k
+  const float4 p2 = ldx<G>(sc.planars + 4 * idx + 2);      // S_alpha
+  const float4 p3 = ldx<G>(sc.planars + 4 * idx + 3);      // S_beta
+  p = along(r.o, t, r.d);
+  const V3 pl = vsub(p, v3(p1.x, p1.y, p1.z));
+  alpha = fmul(p1.w, dot_yfirst(pl, v3(p2.x, p2.y, p2.z)));
+  beta = fmul(p1.w, dot_yfirst(pl, v3(p3.x, p3.y, p3.z)));
+  return (0.0f <= alpha && alpha <= 1.0f) && (0.0f <= beta && beta <= 1.0f);
+}
 // `p0` = first word of the record (normal, d): the linear program carries it inside the op, the other walks load it here
-template <bool EAGER = false, bool G = false>
+template <bool EAGER = false, bool G = false, bool AX = false>
 __device__ __forceinline__ bool planar_t_p0(const Scene &sc, const float4 p0, uint32_t idx, bool triangle, const Ray &r, float tmin,
                                             float tmax, float &t_out) {
   float4 p1 = p0, p2 = p0, p3 = p0;
@@ -152,7 +167,8 @@ __device__ __forceinline__ bool planar_t_p0(const Scene &sc, const float4 p0, ui
   const float t = zero_num ? __uint_as_float((__float_as_uint(num) ^ __float_as_uint(denom)) & 0x80000000u) : quot;
   if (!(tmin <= t && t <= tmax)) return false;
   V3 p; float alpha, beta;
-  if (EAGER ? !planar_inside_rec(p1, p2, p3, triangle, r, t, p, alpha, beta) : !planar_inside<G>(sc, idx, triangle, r, t, p, alpha, beta)) return false;
+  if (AX) { if (!planar_inside_axis<G>(sc, idx, r, t, p, alpha, beta)) return false; }
+  else if (EAGER ? !planar_inside_rec(p1, p2, p3, triangle, r, t, p, alpha, beta) : !planar_inside<G>(sc, idx, triangle, r, t, p, alpha, beta)) return false;
   t_out = t;
   return true;
 }
@@ -161,12 +177,13 @@ __device__ __forceinline__ bool planar_t(const Scene &sc, uint32_t idx, bool tri
                                          float &t_out) {
   return planar_t_p0<EAGER>(sc, ldg4(sc.planars + 4 * idx), idx, triangle, r, tmin, tmax, t_out);
 }
-template <bool G = false>
+template <bool G = false, bool AX = false>
 __device__ __forceinline__ void planar_record_p0(const Scene &sc, const float4 p0, uint32_t idx, const Ray &r, float t, Hit &h) {
   const V3 n = v3(p0.x, p0.y, p0.z);
   const float denom = dot_yfirst(n, r.d);
   float alpha, beta;
-  planar_inside<G>(sc, idx, false, r, t, h.p, alpha, beta);
+  if (AX) planar_inside_axis<G>(sc, idx, r, t, h.p, alpha, beta);
+  else planar_inside<G>(sc, idx, false, r, t, h.p, alpha, beta);
   h.u = alpha; h.v = beta; h.t = t;
   h.front = denom < 0.0f;
   h.n = h.front ? n : vneg(n);
@@ -184,12 +201,12 @@ __device__ __forceinline__ bool hit_planar(const Scene &sc, uint32_t idx, bool t
   tmax = t;
   return true;
 }
-template <bool EAGER = false, bool G = false>
+template <bool EAGER = false, bool G = false, bool AX = false>
 __device__ __forceinline__ bool hit_planar_p0(const Scene &sc, const float4 p0, uint32_t idx, bool triangle, const Ray &r, float tmin,
                                               float &tmax, Hit &h) {
   float t;
-  if (!planar_t_p0<EAGER, G>(sc, p0, idx, triangle, r, tmin, tmax, t)) return false;
-  planar_record_p0<G>(sc, p0, idx, r, t, h);
+  if (!planar_t_p0<EAGER, G, AX>(sc, p0, idx, triangle, r, tmin, tmax, t)) return false;
+  planar_record_p0<G, AX>(sc, p0, idx, r, t, h);
   tmax = t;
   return true;
 }
@@ -446,7 +463,7 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
 // issued once per warp and ray) ran 14 % SLOWER than the stack walk: 7 % fewer warp-instructions, but every step a
 // serial chain vote -> op load -> branch -> test, and the lanes' inside tests no longer overlap across quads.
 constexpr uint32_t OP_T_EXIT = 6u, OP_R_EXIT = 7u, OP_IN_WRAPPER = 0x100u;
-template <bool G = false, class C>
+template <bool G = false, bool AX = false, class C>
 __device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin, float tmax, Hit &h, C &cnt) {
   bool result = false, was_last_hit = false;
   V3 inv = v3(frcp(r.d.x), frcp(r.d.y), frcp(r.d.z));
@@ -478,7 +495,7 @@ __device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin
       case rtd::K_TRIANGLE:
       case rtd::K_QUAD:
         cnt.planar();
-        if (hit_planar_p0<false, G>(sc, w0, arg, (code & 7u) == rtd::K_TRIANGLE, r, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
+        if (hit_planar_p0<false, G, AX>(sc, w0, arg, !AX && (code & 7u) == rtd::K_TRIANGLE, r, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
         break;
       case rtd::K_BVH: {
         float t0 = tmin, t1 = tmax;

@@ -208,6 +208,9 @@ typedef struct rt_pack_info {
   uint32_t instanced_leaves;               /* RT_TRAVERSAL_FAST: leaves of the own BVH that are tested in the primitive's own space
                                               (translation / y-rotation chains around one primitive): the reference's records and
                                               the reference's arithmetic, so the rounding behaviour of its images is kept */
+  uint32_t program_axis_quads;             /* 1: every planar op of the linear program is a quad with axis-aligned normal, u and v
+                                              (walls, boxes): the walk runs their inside test in reduced form -- the same
+                                              roundings with the exact-zero terms left out (env RT_AXIS_QUADS=0 keeps the general form) */
 } rt_pack_info;
 int rt_scene_pack_info(const rt_scene_desc *scene, uint32_t traversal, uint32_t treelet_min, uint32_t fuse_min, rt_pack_info *out);
 

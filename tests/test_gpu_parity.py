@@ -363,7 +363,7 @@ def test_tier2_converged_images_vs_reference_gpu(gpu_ctx, oracle, product_lib, s
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("sid", [2, 17, 0])
+@pytest.mark.parametrize("sid", [2, 17, 0, 1])
 def test_image_does_not_depend_on_scheduling_knobs(product_lib, sid):
     """Chunk size, tile shape, claim grouping, item order (tile order / scattered) and which of the exact walks a scene
     gets only change WHO renders a pixel's samples, when and through which code, never the samples: the image is
@@ -374,8 +374,11 @@ def test_image_does_not_depend_on_scheduling_knobs(product_lib, sid):
     knobs = [{}, {"RT_CHUNK": "5"}, {"RT_CHUNK": "1000000"}, {"RT_CHUNK": "7", "RT_TILE_W": "32", "RT_CLAIM_GROUP": "1"},
              {"RT_CHUNK": "3", "RT_TILE_W": "4", "RT_CLAIM_GROUP": "32"}, {"RT_SCATTER": "0"}, {"RT_SCATTER": "1"},
              {"RT_SCATTER": "1", "RT_CHUNK": "4", "RT_TILE_W": "2", "RT_CLAIM_GROUP": "32"},
-             {"RT_FLAT": "0"}, {"RT_LINEAR": "0"}]                 # scene 17 through its BVH, scene 0 through the stack walk
-    saved = {k: os.environ.get(k) for k in ("RT_CHUNK", "RT_TILE_W", "RT_CLAIM_GROUP", "RT_SCATTER", "RT_FLAT", "RT_LINEAR")}
+             {"RT_FLAT": "0"}, {"RT_LINEAR": "0"},                 # scene 17 through its BVH, scenes 0 / 1 through the stack walk
+             {"RT_AXIS_QUADS": "0"}, {"RT_FUSE_PROGRAM_WRAPPERS": "0"},   # scene 1: general inside test; one op per wrapper side
+             {"RT_AXIS_QUADS": "0", "RT_FUSE_PROGRAM_WRAPPERS": "0", "RT_CHUNK": "6"}]
+    saved = {k: os.environ.get(k) for k in ("RT_CHUNK", "RT_TILE_W", "RT_CLAIM_GROUP", "RT_SCATTER", "RT_FLAT", "RT_LINEAR", "RT_AXIS_QUADS",
+                                            "RT_FUSE_PROGRAM_WRAPPERS")}
     try:
         for kn in knobs:
             for k in saved:

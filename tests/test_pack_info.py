@@ -24,6 +24,19 @@ def test_every_scene_packs_in_every_mode(product_lib, sid):
     hs.close()
 
 
+def test_axis_aligned_quads_are_found_where_every_planar_of_the_program_is_one(product_lib):
+    """Cornell box (scene 1): 6 walls + 2 instanced boxes of 6 quads, all axis-aligned in their own space -> reduced inside test;
+    scene 0 has a pyramid of triangles in its program, the others spheres only or no program at all."""
+    for sid in range(20):
+        hs = product_lib.HostScene(sid)
+        i = hs.pack_info()
+        assert i.program_axis_quads == (1 if sid == 1 else 0), sid
+        if sid == 1:
+            assert (i.kernel_mode, i.planars, i.spheres) == (3, 18, 0)
+            assert hs.pack_info(product_lib.RT_TRAVERSAL_REFERENCE).program_axis_quads == 0      # no program, no reduced form
+        hs.close()
+
+
 def test_final_scene_gets_treelets_and_fused_instances(product_lib):
     """Scene 3: 400 ground boxes (2400 quads) + light + 5 spheres at top level, 1000 spheres each in translate(rotate())."""
     hs = product_lib.HostScene(3)

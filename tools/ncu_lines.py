@@ -13,6 +13,7 @@ from collections import defaultdict
 
 
 INCLUSIVE = False
+INNER = False       # --inner (with --frame): the INNERMOST frame inside FILE instead of the outermost
 FRAME = None        # --frame FILE: attribute an instruction to its outermost inlining frame inside FILE (implies -gi)
 
 
@@ -39,7 +40,7 @@ def line_map(obj, kernel):
             cur = chain[-1]
             if FRAME:
                 inside = [c for c in chain if c[0] == FRAME]
-                cur = inside[-1] if inside else chain[-1]
+                cur = (inside[0] if INNER else inside[-1]) if inside else chain[-1]
             continue
         m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(.*?);", ln)
         if m:
@@ -53,7 +54,10 @@ def main():
     if "--inclusive" in sys.argv:          # attribute inlined code to the outermost call site
         INCLUSIVE = True
         sys.argv.remove("--inclusive")
-    global FRAME
+    global FRAME, INNER
+    if "--inner" in sys.argv:
+        INNER = True
+        sys.argv.remove("--inner")
     if "--frame" in sys.argv:              # e.g. --frame rt_trace.cuh: per line of the walk instead of per line of the kernel body
         i = sys.argv.index("--frame")
         FRAME = sys.argv[i + 1]
