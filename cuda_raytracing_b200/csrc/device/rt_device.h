@@ -71,6 +71,9 @@ struct Scene {
   //                              {0,0, sphere / planar index, K_SPHERE|K_TRIANGLE|K_QUAD (| OP_IN_WRAPPER)}
   //   translation  {offset,0}    {0,0,0, K_TRANSLATION (way in) | OP_T_EXIT (way out)}
   //   y-rotation   {sin,cos,0,0} {0,0,0, K_YROTATION (way in) | OP_R_EXIT (way out)}
+  //   translate(rotate(x)) as one op each way (OP_FUSED_WRAPPER = 0x200):
+  //                {offset,0}    {sin,cos,0, K_TRANSLATION | 0x200}         way in: translate, then rotate
+  //                {sin,cos,offset.xy} {offset.z,0,0, OP_R_EXIT | 0x200}    way out: un-rotate, then un-translate
   const float4 *program;
   uint32_t program_ops;         // 0: the scene has no program (too big, or wrappers nested in a way only the stack walk mirrors)
   uint32_t stack_entries;       // traversal stack entries per thread this scene's walk can need (<= STACK_CAPACITY)

@@ -7,6 +7,7 @@
 
 #include <math.h>
 #include <cmath>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -176,9 +177,12 @@ struct Packer {
   bool fuse_instances;
   uint32_t fuse_min;                            // fewer qualifying chains than this (and no treelet): keep the plain walk
   uint32_t program_max;                         // longest reference-order walk (ops) laid out as a linear program; 0 = never
+  bool fuse_program_wrappers = true;            // env RT_FUSE_PROGRAM_WRAPPERS=0 keeps one op per wrapper side (bisecting)
   mutable bool too_deep = false;                // a recursion below hit its nesting guard: the scene is refused, never truncated
   Packer(const rt_scene_desc &desc, PackedScene &o, uint32_t tmin, uint32_t fmin, uint32_t pmax)
-      : d(desc), out(o), treelet_min(tmin), fuse_instances(fmin > 0), fuse_min(fmin), program_max(pmax) {}
+      : d(desc), out(o), treelet_min(tmin), fuse_instances(fmin > 0), fuse_min(fmin), program_max(pmax) {
+    if (const char *v = getenv("RT_FUSE_PROGRAM_WRAPPERS")) fuse_program_wrappers = strtol(v, nullptr, 10) != 0;
+  }
 
   const rt_hittable &H(uint32_t i) const { return d.hittables[i]; }
 
@@ -441,6 +445,18 @@ struct Packer {
       case RT_OBJ_TRANSLATION: {
         if (in_t) return false;
         const rt_vec3 &o = h.u.translation.offset;
+        // translate(rotate(x)) -- every instanced box of the reference's scenes -- as ONE op each way: the two ways in follow
+        // each other without anything in between, and so do the two ways out, so the ops do the same arithmetic in the same
+        // order and a lane spends two steps of the walk less per instance side (OP_FUSED_WRAPPER, rt_trace.cuh)
+        if (fuse_program_wrappers && !in_r && h.u.translation.child < d.hittable_count && H(h.u.translation.child).type == RT_OBJ_Y_ROTATION) {
+          const rt_hittable &rot = H(h.u.translation.child);
+          const float sn = rot.u.y_rotation.sin_theta, cs = rot.u.y_rotation.cos_theta;
+          program_op(f4(o.x, o.y, o.z, 0), sn, cs, 0, K_TRANSLATION | 0x200u);
+          out.program_wrappers += 2;
+          if (!emit_program(rot.u.y_rotation.child, true, true, guard + 2)) return false;
+          program_op(f4(sn, cs, o.x, o.y), o.z, 0, 0, 7u | 0x200u);
+          return out.program.size() / 2 <= program_max;
+        }
         program_op(f4(o.x, o.y, o.z, 0), 0, 0, 0, K_TRANSLATION);
         ++out.program_wrappers;
         if (!emit_program(h.u.translation.child, true, in_r, guard + 1)) return false;

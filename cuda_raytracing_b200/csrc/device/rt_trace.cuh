@@ -462,7 +462,7 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
 // A variant that walked the program in lockstep (every step the lowest op any lane has to do, redux.sync min; each op
 // issued once per warp and ray) ran 14 % SLOWER than the stack walk: 7 % fewer warp-instructions, but every step a
 // serial chain vote -> op load -> branch -> test, and the lanes' inside tests no longer overlap across quads.
-constexpr uint32_t OP_T_EXIT = 6u, OP_R_EXIT = 7u, OP_IN_WRAPPER = 0x100u;
+constexpr uint32_t OP_T_EXIT = 6u, OP_R_EXIT = 7u, OP_IN_WRAPPER = 0x100u, OP_FUSED_WRAPPER = 0x200u;
 template <bool G = false, bool AX = false, class C>
 __device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin, float tmax, Hit &h, C &cnt) {
   bool result = false, was_last_hit = false;
@@ -514,6 +514,15 @@ __device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin
         cnt.translation();
         was_last_hit = false;
         r.o = vsub(r.o, v3(w0.x, w0.y, w0.z));
+        if (code & OP_FUSED_WRAPPER) {                        // translate(rotate(x)): the rotation's way in follows at once
+          const float sn = w1.x, cs = w1.y;
+          cnt.rotation();
+          const V3 o = r.o, d = r.d;
+          r.o = v3(ffma(o.x, cs, -fmul(o.z, sn)), o.y, ffma(o.x, sn, fmul(o.z, cs)));
+          r.d = v3(ffma(d.x, cs, -fmul(d.z, sn)), d.y, ffma(d.z, cs, fmul(d.x, sn)));
+          inv.x = frcp(r.d.x); inv.z = frcp(r.d.z);
+          a = dot_xfirst(r.d, r.d);
+        }
         break;
       case OP_T_EXIT: {
         const V3 off = v3(w0.x, w0.y, w0.z);
@@ -544,6 +553,12 @@ __device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin
         }
         inv.x = frcp(r.d.x); inv.z = frcp(r.d.z);
         a = dot_xfirst(r.d, r.d);
+        if (code & OP_FUSED_WRAPPER) {                        // ... and the translation's way out follows the rotation's
+          const V3 off = v3(w0.z, w0.w, w1.x);
+          cnt.translation();
+          r.o = vadd(r.o, off);
+          if (was_last_hit) h.p = vadd(h.p, off);
+        }
       } break;
     }
   }

@@ -86,12 +86,16 @@ def run_program(ops, seed):
                 nxt = arg
         elif kind == TRANSLATION:
             events.append(("t_in", f[pc, :3].tobytes()))
+            if code & 0x200:                                                # translate(rotate(x)) as one op: {offset,0} {sin,cos,..}
+                events.append(("r_in", f[pc, 4:6].tobytes()))
         elif kind == 6:
             events.append(("t_out", f[pc, :3].tobytes()))
         elif kind == YROTATION:
             events.append(("r_in", f[pc, :2].tobytes()))
         else:
             events.append(("r_out", f[pc, :2].tobytes()))
+            if code & 0x200:                                                # ... and the way out: {sin,cos,offset.xy} {offset.z,..}
+                events.append(("t_out", f[pc, 2:5].tobytes()))
         pc = nxt
     return events
 

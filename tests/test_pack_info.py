@@ -1,5 +1,7 @@
 """Host logic of the packer (no GPU): which walk a scene gets, what the treelet / fused-instance planting finds, and
 that every built-in scene fits the device limits in every traversal mode (rt_scene_pack_info, host only)."""
+import os
+
 import pytest
 
 
@@ -75,9 +77,19 @@ def test_linear_program_of_the_cornell_box(product_lib):
     translate(rotate(structure of 6 quads)), a structure costs no op (its children are simply walked)."""
     hs = product_lib.HostScene(1)
     i = hs.pack_info()
-    assert i.kernel_mode == 3 and i.program_ops == i.program_boxes + i.program_prims + 2 * i.program_wrappers
+    assert i.kernel_mode == 3
     assert i.program_boxes == 7 and i.program_wrappers == 2 * 2 and i.program_prims == 6 + 2 * 6
-    assert i.program_ops == 33                                  # every wrapper is a way in and a way out
+    # a wrapper is a way in and a way out; translate(rotate(x)) is ONE op each way (the two ways in follow each other at once)
+    assert i.program_ops == i.program_boxes + i.program_prims + i.program_wrappers == 29
+    saved = os.environ.get("RT_FUSE_PROGRAM_WRAPPERS")
+    os.environ["RT_FUSE_PROGRAM_WRAPPERS"] = "0"                # one op per wrapper side, as before
+    try:
+        j = hs.pack_info()
+    finally:
+        os.environ.pop("RT_FUSE_PROGRAM_WRAPPERS")
+        if saved is not None:
+            os.environ["RT_FUSE_PROGRAM_WRAPPERS"] = saved
+    assert j.program_ops == j.program_boxes + j.program_prims + 2 * j.program_wrappers == 33
     big = product_lib.HostScene(3).pack_info()                  # 7593 objects: far beyond the program limit, and it has treelets
     assert big.kernel_mode == 2 and big.program_ops == 0
     hs.close()
