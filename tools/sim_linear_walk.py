@@ -10,6 +10,7 @@ schedules.  Float64 numpy, no claim of bit-exactness: only the statistics of who
   P1  kind-ordered sweep: an iteration runs the blocks in a fixed order and a lane may pass through several of them
   P2  P0 with the wrappers fused (translate+rotate one op, un-rotate+un-translate one op)
   P3  P1 with the wrappers fused
+  P4  majority vote: every iteration runs ONE block, the kind most lanes wait at (P4f: with the wrappers fused)
 usage: sim_linear_walk.py [warps=40] [bounce_steps=60]
 """
 import os
@@ -53,7 +54,7 @@ def load_program():
     for op in prog:
         u = op.view(np.uint32)
         f = op.view(np.float32).astype(np.float64)
-        ops.append(dict(kind=int(u[7] & 7), arg=int(u[6]), f=f))
+        ops.append(dict(kind=int(u[7] & 7), fused=bool(u[7] & 0x200), arg=int(u[6]), f=f))
     return ops
 
 
@@ -98,8 +99,12 @@ def trace(ops, quads, o, d):
                         in_wrap_hit = len(stack) > 0
             seq.append((K_QUAD, ph))
         elif k == K_T:
-            seq.append((K_T, 0)); in_wrap_hit = False
+            seq.append((K_T, 1 if op["fused"] else 0)); in_wrap_hit = False
             o = o - f[0:3]; stack.append(1)
+            if op["fused"]:                                    # translate(rotate(x)) as one op: {offset,0} {sin,cos,..}
+                sn, cs = f[4], f[5]
+                o = np.array([o[0] * cs - o[2] * sn, o[1], o[0] * sn + o[2] * cs])
+                d = np.array([d[0] * cs - d[2] * sn, d[1], d[2] * cs + d[0] * sn])
         elif k == K_TX:
             seq.append((K_TX, 0))
             o = o + f[0:3]
@@ -118,6 +123,12 @@ def trace(ops, quads, o, d):
             o, d = rot(o), rot(d)
             if in_wrap_hit:
                 hit["p"], hit["n"] = rot(hit["p"]), rot(hit["n"])
+            if op["fused"]:                                    # ... and the way out: {sin,cos,offset.xy} {offset.z,..}
+                seq[-1] = (K_RX, 1)
+                o = o + f[2:5]
+                if in_wrap_hit:
+                    hit["p"] = hit["p"] + f[2:5]
+                stack.pop()
         else:
             raise RuntimeError("unexpected op kind %d" % k)
     return seq, hit
@@ -229,11 +240,31 @@ def cost_sweep(seqs, order):
     return tot, iters
 
 
+def cost_majority(seqs, vote=14.0, weight=None):
+    """every iteration ONE block: the kind most lanes are waiting at (ties: the cheaper block); the others hold their op"""
+    pos = [0] * len(seqs)
+    tot, iters = 0.0, 0
+    while True:
+        present = {}
+        for j, s in enumerate(seqs):
+            if pos[j] < len(s):
+                present.setdefault(s[pos[j]][0], []).append(j)
+        if not present:
+            break
+        iters += 1
+        k = max(present, key=lambda x: (len(present[x]) * (weight[x] if weight else 1.0), -block_cost(x, [seqs[j][pos[j]] for j in present[x]])))
+        items = [seqs[j][pos[j]] for j in present[k]]
+        tot += COST["loop"] + vote + block_cost(k, items)
+        for j in present[k]:
+            pos[j] += 1
+    return tot, iters
+
+
 def main():
     warps = int(sys.argv[1]) if len(sys.argv) > 1 else 40
     steps = int(sys.argv[2]) if len(sys.argv) > 2 else 60
     ops, quads = load_program(), cornell_quads()
-    res = {k: 0.0 for k in ("P0", "P1", "P1b", "P2", "P3", "P3b")}
+    res = {k: 0.0 for k in ("P0", "P1", "P1b", "P2", "P3", "P3b", "P4", "P4f", "P4w")}
     iters = {k: 0 for k in res}
     parts_tot, lane_ops, n_steps = {}, 0, 0
     lens = []
@@ -257,6 +288,9 @@ def main():
             c, n, _ = cost_p0(f); res["P2"] += c; iters["P2"] += n
             c, n = cost_sweep(f, (K_T, K_BVH, K_QUAD, K_RX)); res["P3"] += c; iters["P3"] += n
             c, n = cost_sweep(f, (K_BVH, K_T, K_QUAD, K_RX)); res["P3b"] += c; iters["P3b"] += n
+            c, n = cost_majority(seqs); res["P4"] += c; iters["P4"] += n
+            c, n = cost_majority(f); res["P4f"] += c; iters["P4f"] += n
+            c, n = cost_majority(f, weight={K_BVH: 0.5, K_QUAD: 1.0, K_T: 0.7, K_R: 0.7, K_RX: 0.7, K_TX: 0.7}); res["P4w"] += c; iters["P4w"] += n
     print("warp-bounces %d, ops per lane %.1f (min %d, max %d)" % (n_steps, lane_ops / n_steps / 32.0, min(lens), max(lens)))
     names = {K_BVH: "box", K_QUAD: "planar", K_T: "translate", K_R: "rotate", K_RX: "un-rotate", K_TX: "un-translate", "loop": "loop"}
     print("P0 parts per warp-bounce:", {names[k]: round(v / n_steps, 1) for k, v in parts_tot.items()})
