@@ -101,6 +101,13 @@ struct Scene {
   uint64_t tex_bytes;
 };
 
+// The linear program and the primitive records it reads are staged in shared memory by the kernels of modes 3 / 4; the
+// packer only keeps a program whose staging area fits (256 ops of 32 B + their primitives: 24 KB at most)
+constexpr uint32_t LINEAR_SMEM_MAX_BYTES = 24576;
+RTD_HD uint32_t linear_stage_bytes(uint32_t program_ops, uint32_t planar_count, uint32_t sphere_count) {
+  return 32u * program_ops + 64u * planar_count + 32u * sphere_count;
+}
+
 constexpr int MAX_CHUNK_TABLE = 32;
 
 struct RenderArgs {

@@ -75,10 +75,8 @@ __device__ __forceinline__ void st_volatile_u32(uint32_t *p, uint32_t v) { *rein
 // kernel modes 3 / 4 with RT_LINEAR_SMEM: the linear program, the planar and the sphere records of the (small) scene are
 // staged in shared memory when they fit, and the walk reads them with generic loads (measured, r2i_linear_program_in_smem.jsonl:
 // Cornell box s1024 309.6 -> 306.1 ms, s128 42.6 -> 41.6 ms, scene 0 1.100 -> 1.071 ms; RT_LINEAR_SMEM=0 builds the global-memory walk)
-constexpr uint32_t LINEAR_SMEM_MAX_BYTES = 16384;
 __host__ __device__ inline uint32_t linear_smem_bytes(const Scene &sc) {
-  const uint32_t b = 32u * sc.program_ops + 64u * sc.planar_count + 32u * sc.sphere_count;
-  return (RT_LINEAR_SMEM && sc.program_ops > 0 && b <= LINEAR_SMEM_MAX_BYTES) ? b : 0u;
+  return (RT_LINEAR_SMEM && sc.program_ops > 0) ? rtd::linear_stage_bytes(sc.program_ops, sc.planar_count, sc.sphere_count) : 0u;
 }
 
 template <int MODE, bool AX, class C>
@@ -113,7 +111,9 @@ __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(cons
 #if RT_LINEAR_SMEM
   Scene sc = a.scene;
   if (AX) sc.planars = a.scene.planars_axis;
-  if ((MODE == 3 || MODE == 4) && linear_smem_bytes(a.scene) > 0) {         // block-uniform; the staging area is the last part of smem
+  // unconditional (the packer keeps a program only if this fits): the walk's pointers are then shared-memory pointers at
+  // compile time, and its loads LDS with an immediate offset instead of generic loads behind a 64-bit address computation
+  if (MODE == 3 || MODE == 4) {                                              // the staging area is the last part of smem
     float4 *dst = reinterpret_cast<float4 *>(smem + a.linear_smem_word);
     const uint32_t n_prog = 2u * sc.program_ops, n_plan = 4u * sc.planar_count, n_sph = 2u * sc.sphere_count;
     for (uint32_t i = threadIdx.x; i < n_prog; i += blockDim.x) dst[i] = __ldg(a.scene.program + i);

@@ -643,6 +643,10 @@ struct Packer {
       out.program.clear(); out.program_boxes = out.program_prims = out.program_wrappers = 0;
     }
 
+    if (!out.program.empty() &&
+        linear_stage_bytes((uint32_t)(out.program.size() / 2), (uint32_t)(out.planars.size() / 4), (uint32_t)(out.spheres.size() / 2)) > LINEAR_SMEM_MAX_BYTES) {
+      out.program.clear(); out.program_boxes = out.program_prims = out.program_wrappers = 0;   // would not fit its staging area
+    }
     if (!out.program.empty()) axis_aligned_words();
 
     // own BVH over the whole scene
