@@ -16,10 +16,6 @@
 #define RT_PUSH(v) (stk[(sp++) * stride] = (v))
 #endif
 
-#ifndef RT_LINEAR_PREFETCH
-#define RT_LINEAR_PREFETCH 0
-#endif
-
 namespace rtt {
 using namespace rtm;
 using rtd::Scene;
@@ -468,25 +464,14 @@ __device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin
   bool result = false, was_last_hit = false;
   V3 inv = v3(frcp(r.d.x), frcp(r.d.y), frcp(r.d.z));
   float a = dot_xfirst(r.d, r.d);
-  const uint32_t n_ops = sc.program_ops;
-  uint32_t pc = 0;
-#if RT_LINEAR_PREFETCH
-  // the op that follows is requested while this one is worked on (a missed box throws it away and loads its skip target):
-  // the walk is one dependent L1 load per step otherwise (measured: 21 % of the stall samples on the first use of the op)
-  float4 nx0 = ldg4(sc.program), nx1 = ldg4(sc.program + 1);
-#endif
-  while (pc < n_ops) {
-#if RT_LINEAR_PREFETCH
-    const float4 w0 = nx0, w1 = nx1;
-    {
-      const uint32_t nx = pc + 1 < n_ops ? pc + 1 : pc;
-      nx0 = ldg4(sc.program + 2 * nx); nx1 = ldg4(sc.program + 2 * nx + 1);
-    }
-#else
-    const float4 w0 = ldx<G>(sc.program + 2 * pc), w1 = ldx<G>(sc.program + 2 * pc + 1);
-#endif
+  // the walk keeps the ADDRESS of its next op (in the kernels of modes 3 / 4 a 32-bit shared-memory address: two LDS.128 with
+  // immediate offsets and one add per step, no index arithmetic)
+  const float4 *op = sc.program;
+  const float4 *const end = sc.program + 2 * sc.program_ops;
+  while (op < end) {
+    const float4 w0 = ldx<G>(op), w1 = ldx<G>(op + 1);
     const uint32_t code = __float_as_uint(w1.w), arg = __float_as_uint(w1.z);
-    ++pc;
+    op += 2;
     switch (code & 7u) {
       case rtd::K_SPHERE:
         cnt.sphere();
@@ -503,12 +488,7 @@ __device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin
         const bool ax = aabb_axis(w0.x, w0.y, r.o.x, inv.x, t0, t1);
         const bool ay = aabb_axis(w0.z, w0.w, r.o.y, inv.y, t0, t1);
         const bool az = aabb_axis(w1.x, w1.y, r.o.z, inv.z, t0, t1);
-        if (!(ax & ay & az)) {
-          pc = arg;
-#if RT_LINEAR_PREFETCH
-          if (pc < n_ops) { nx0 = ldg4(sc.program + 2 * pc); nx1 = ldg4(sc.program + 2 * pc + 1); }
-#endif
-        }
+        if (!(ax & ay & az)) op = sc.program + 2 * arg;
       } break;
       case rtd::K_TRANSLATION:
         cnt.translation();

@@ -1,5 +1,5 @@
 #!/usr/bin/env bash
-# Round 2, GPU call U: linear walk with compile-time shared-memory pointers (LDS instead of generic loads); before: C4 281.2-281.9, C4s 38.67, C1 1.033 ms
+# Round 2, GPU call U (second run): linear walk keeps the address of its next op; before: C4 279.5-283, C4s 38.27, C4t 20.64, C1 0.977 ms
 set -u
 mkdir -p gpurun_out
 K="python tools/gpu_knobs.py"
