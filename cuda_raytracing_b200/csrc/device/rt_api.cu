@@ -72,6 +72,7 @@ int rt_context_create(int device_id, rt_context **out) {
   if (const char *v = getenv("RT_FLAT")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->flat = (int)x; }
   if (const char *v = getenv("RT_SCATTER")) { const long x = strtol(v, nullptr, 10); if (x >= -1 && x <= 1) ctx->scatter = (int)x; }
   if (const char *v = getenv("RT_AXIS_QUADS")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= 1) ctx->axis_quads = (int)x; }
+  if (const char *v = getenv("RT_TAIL_MIN")) { const long x = strtol(v, nullptr, 10); if (x >= 1 && x <= 4096) ctx->tail_min = (int)x; }
   if (const char *v = getenv("RT_FIRST_CHUNK")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= (1 << 24)) ctx->first_chunk = (int)x; }
   if (const char *v = getenv("RT_CLAIM_GROUP")) { const long x = strtol(v, nullptr, 10); if (x >= 0 && x <= 32) ctx->claim_group = (int)x; }
   std::vector<uint32_t> mats;
@@ -226,7 +227,7 @@ static int render_set(rt_context *ctx, const rt_render_params *p, int row0, int 
 }
 
 // ---- the scheduling decisions of a render: host logic only, shared by rt_render_device and rt_render_plan_query ----
-struct PlanKnobs { int chunk_samples = 0, claim_group = 0, scatter = -1, tile_w = 8, first_chunk = 0; };
+struct PlanKnobs { int chunk_samples = 0, claim_group = 0, scatter = -1, tile_w = 8, first_chunk = 0, tail_min = 8; };
 static void plan_render(int packed_mode, uint32_t traversal_used, uint32_t prims, int32_t img_width, uint32_t rows, int32_t samples_per_pixel,
                         int bounces, int sm_count, const PlanKnobs &kn, rt_render_plan *out) {
   memset(out, 0, sizeof(*out));
@@ -296,7 +297,7 @@ static void plan_render(int packed_mode, uint32_t traversal_used, uint32_t prims
   } else {
     if (kn.first_chunk > 0 && kn.first_chunk < bulk) { done = kn.first_chunk; out->chunk_begin[++n] = done; }   // RT_FIRST_CHUNK (experiments)
     while (spp - done > 2 * bulk && n < rtd::MAX_CHUNK_TABLE - 6) { done += bulk; out->chunk_begin[++n] = done; }
-    while (spp - done >= 16 && n < rtd::MAX_CHUNK_TABLE - 1) { done += (spp - done + 1) / 2; out->chunk_begin[++n] = done; }
+    while (spp - done >= 2 * kn.tail_min && n < rtd::MAX_CHUNK_TABLE - 1) { done += (spp - done + 1) / 2; out->chunk_begin[++n] = done; }
     if (spp - done > 0) { done = spp; out->chunk_begin[++n] = done; }
   }
   out->chunk_count = (uint32_t)n;
@@ -367,7 +368,7 @@ int rt_render_device(rt_context *ctx, const rt_render_params *p, float *d_pixels
   const int bounces = p->max_bounces & 255;                // u8 counter of the reference (rt.cu:220)
   PlanKnobs knobs;
   knobs.chunk_samples = ctx->chunk_samples; knobs.claim_group = ctx->claim_group; knobs.scatter = ctx->scatter; knobs.tile_w = ctx->tile_w;
-  knobs.first_chunk = ctx->first_chunk;
+  knobs.first_chunk = ctx->first_chunk; knobs.tail_min = ctx->tail_min;
   rt_render_plan plan;
   plan_render(kernel_mode(ctx->packed), ctx->packed.traversal_used, ctx->packed.sphere_count + ctx->packed.planar_count, p->img_width, set_rows,
               p->samples_per_pixel, bounces, ctx->sm_count, knobs, &plan);
@@ -712,7 +713,7 @@ extern "C" int rt_render_device_static(rt_context *ctx, const rt_render_params *
   const int bounces = p->max_bounces & 255;
   PlanKnobs knobs;
   knobs.chunk_samples = ctx->chunk_samples; knobs.claim_group = ctx->claim_group; knobs.scatter = ctx->scatter; knobs.tile_w = ctx->tile_w;
-  knobs.first_chunk = ctx->first_chunk;
+  knobs.first_chunk = ctx->first_chunk; knobs.tail_min = ctx->tail_min;
   rt_render_plan plan;
   plan_render(kernel_mode(ctx->packed), ctx->packed.traversal_used, ctx->packed.sphere_count + ctx->packed.planar_count, p->img_width, set.rows,
               p->samples_per_pixel, bounces, ctx->sm_count, knobs, &plan);

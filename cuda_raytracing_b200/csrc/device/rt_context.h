@@ -56,6 +56,7 @@ struct rt_context {
   int chunk_samples = 0;                                   // 0 = automatic; env RT_CHUNK overrides (tuning knob)
   int claim_group = 0;                                     // 0 = automatic; env RT_CLAIM_GROUP (tuning knob)
   int axis_quads = 1;                                      // env RT_AXIS_QUADS=0: keep the general inside test for axis-aligned quads (bisecting)
+  int tail_min = 8;                                        // env RT_TAIL_MIN: the halving tail of the chunk schedule stops at this many samples
   int first_chunk = 0;                                     // env RT_FIRST_CHUNK: a short first chunk in front of the schedule (experiments)
   uint32_t fuse_min = 8;                                   // env RT_FUSE_MIN: wrapper chains around one object become one item when there are this many (0 = never)
   uint32_t treelet_min = 8;                                // env RT_TREELET_MIN: smallest wrapper-free subtree given an own BVH (0 = none)

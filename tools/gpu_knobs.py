@@ -16,7 +16,7 @@ import cuda_raytracing_b200 as rt  # noqa: E402
 CONFIGS = {"C1": (0, 16, 8, 0), "C2": (2, 256, 50, 0), "C3": (17, 512, 50, 0), "C3b": (19, 512, 50, 0), "C4": (1, 1024, 50, 0),
            "C4h": (1, 512, 50, 0), "C4q": (1, 256, 50, 0), "C4s": (1, 128, 50, 0), "C4t": (1, 64, 50, 0),
            "C5s": (3, 16, 50, 0), "C5m": (3, 64, 50, 0), "C5w": (3, 16, 50, 3840)}
-NAMES = ("RT_SCATTER", "RT_CHUNK", "RT_CLAIM_GROUP", "RT_TILE_W", "RT_FUSE_MIN", "RT_TREELET_MIN", "RT_CARVEOUT", "RT_LINEAR", "RT_BLOCKS_PER_SM", "RT_FLAT", "RT_AXIS_QUADS", "RT_FUSE_PROGRAM_WRAPPERS")
+NAMES = ("RT_SCATTER", "RT_CHUNK", "RT_CLAIM_GROUP", "RT_TILE_W", "RT_FUSE_MIN", "RT_TREELET_MIN", "RT_CARVEOUT", "RT_LINEAR", "RT_BLOCKS_PER_SM", "RT_FLAT", "RT_AXIS_QUADS", "RT_FUSE_PROGRAM_WRAPPERS", "RT_TAIL_MIN")
 
 
 def main():
