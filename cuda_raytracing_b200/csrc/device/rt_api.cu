@@ -90,7 +90,7 @@ void rt_context_destroy(rt_context *ctx) {
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   DeviceBuffer *all[] = {&ctx->b_ref_nodes, &ctx->b_xforms, &ctx->b_instances, &ctx->b_structs, &ctx->b_struct_children, &ctx->b_fast_nodes,
-                         &ctx->b_spheres, &ctx->b_planars, &ctx->b_planars_axis, &ctx->b_materials, &ctx->b_checkers, &ctx->b_perlin_vec,
+                         &ctx->b_spheres, &ctx->b_planars, &ctx->b_materials, &ctx->b_checkers, &ctx->b_perlin_vec,
                          &ctx->b_perlin_perm, &ctx->b_arena, &ctx->b_program, &ctx->b_rng_mats, &ctx->b_rng_init, &ctx->b_rng_states,
                          &ctx->b_progress, &ctx->b_counters,
                          &ctx->b_pixels, &ctx->b_rgb8};
@@ -141,17 +141,20 @@ int rtc::upload_packed(rt_context *ctx, const rtp::PackedScene &packed) {
   UP(b_ref_nodes, p.ref_nodes); UP(b_xforms, p.xforms); UP(b_instances, p.instances); UP(b_structs, p.structures); UP(b_struct_children, p.struct_children);
   UP(b_fast_nodes, p.fast_nodes); UP(b_spheres, p.spheres); UP(b_planars, p.planars); UP(b_materials, p.materials);
   UP(b_checkers, p.checkers); UP(b_perlin_vec, p.perlin_vectors); UP(b_perlin_perm, p.perlin_perm); UP(b_arena, p.tex_arena);
-  UP(b_program, p.program); UP(b_planars_axis, p.planars_axis);
+  std::vector<float4> image;                               // the linear program as the kernels walk it (ops + records, one block)
+  const bool axis = p.program_axis_quads && ctx->axis_quads != 0;
+  rtp::build_linear_image(p, axis, image);
+  UP(b_program, image);
 #undef UP
   RT_CUDA(ctx, cudaStreamSynchronize(s));       // the host vectors may be reused after return
   rtd::Scene &sc = ctx->scene;
   sc.ref_nodes = (const float4 *)ctx->b_ref_nodes.ptr; sc.xforms = (const float4 *)ctx->b_xforms.ptr;
   sc.instances = (const float4 *)ctx->b_instances.ptr;
   sc.structures = (const uint2 *)ctx->b_structs.ptr; sc.struct_children = (const uint32_t *)ctx->b_struct_children.ptr;
-  sc.program = (const float4 *)ctx->b_program.ptr; sc.program_ops = (uint32_t)(p.program.size() / 2);
+  sc.program = (const float4 *)ctx->b_program.ptr; sc.program_ops = p.program.empty() ? 0u : (uint32_t)(p.program.size() / 2 + 1);
+  sc.linear_float4s = (uint32_t)image.size(); sc.linear_axis = axis ? 1u : 0u;
   sc.ref_root = p.ref_root; sc.fast_nodes = (const float4 *)ctx->b_fast_nodes.ptr; sc.fast_root = p.fast_root;
   sc.spheres = (const float4 *)ctx->b_spheres.ptr; sc.planars = (const float4 *)ctx->b_planars.ptr;
-  sc.planars_axis = (p.program_axis_quads && ctx->axis_quads != 0) ? (const float4 *)ctx->b_planars_axis.ptr : nullptr;
   sc.sphere_count = p.sphere_count; sc.planar_count = p.planar_count; sc.flat_triangles = p.flat_triangles;
   sc.materials = (const uint4 *)ctx->b_materials.ptr; sc.checkers = (const float4 *)ctx->b_checkers.ptr;
   sc.perlin_vectors = (const float4 *)ctx->b_perlin_vec.ptr; sc.perlin_perm = (const uint8_t *)ctx->b_perlin_perm.ptr;

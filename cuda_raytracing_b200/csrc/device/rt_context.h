@@ -49,7 +49,7 @@ struct rt_context {
   bool has_scene = false;
   rtd::Scene scene{};
   rtp::PackedScene packed;
-  rtc::DeviceBuffer b_ref_nodes, b_xforms, b_instances, b_structs, b_struct_children, b_fast_nodes, b_spheres, b_planars, b_planars_axis, b_materials,
+  rtc::DeviceBuffer b_ref_nodes, b_xforms, b_instances, b_structs, b_struct_children, b_fast_nodes, b_spheres, b_planars, b_materials,
       b_checkers, b_perlin_vec, b_perlin_perm, b_arena, b_program;
   // rng
   rtc::DeviceBuffer b_rng_mats, b_rng_init, b_rng_states, b_progress, b_counters;   // b_rng_init: pristine states (cache)

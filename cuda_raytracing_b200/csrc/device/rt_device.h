@@ -65,17 +65,24 @@ struct Scene {
   const uint32_t *struct_children;
   const float4 *instances;      // 2 per fused instance: {offset.xyz, child ref} {sin, cos, INST_* flags, 0}
   uint32_t ref_root;            // tagged ref of the reference's root BVH node
-  // the same walk as a linear program (small scenes; trace_linear): 2 x float4 per op, op i is followed by op i + 1
-  //   box          {x0,x1,y0,y1} {z0,z1, skip op (a missed box continues there), K_BVH}
+  // the same walk as a linear program (small scenes; trace_linear).  `program` points at the program's IMAGE (built at upload,
+  // rt_pack.cpp build_linear_image): the ops, 2 x float4 each, op i followed by op i + 1, then the planar and the sphere records
+  // the ops test -- one block that the kernels of modes 3 / 4 copy to shared memory, addressed RELATIVE to the op at hand
+  // (byte offsets inside the ops), so that the walk needs no base address:
+  //   box          {x0,x1,y0,y1} {z0,z1, byte offset to the op a missed box continues at, K_BVH}
   //   primitive    {n.xyz, d} of a quad / triangle (its record's first word), 0 for a sphere
-  //                              {0,0, sphere / planar index, K_SPHERE|K_TRIANGLE|K_QUAD (| OP_IN_WRAPPER)}
+  //                              {byte offset to its record, 0, sphere / planar index, K_SPHERE|K_TRIANGLE|K_QUAD (| OP_IN_WRAPPER)}
   //   translation  {offset,0}    {0,0,0, K_TRANSLATION (way in) | OP_T_EXIT (way out)}
   //   y-rotation   {sin,cos,0,0} {0,0,0, K_YROTATION (way in) | OP_R_EXIT (way out)}
   //   translate(rotate(x)) as one op each way (OP_FUSED_WRAPPER = 0x200):
   //                {offset,0}    {sin,cos,0, K_TRANSLATION | 0x200}         way in: translate, then rotate
   //                {sin,cos,offset.xy} {offset.z,0,0, OP_R_EXIT | 0x200}    way out: un-rotate, then un-translate
+  //   end          {0} {0,0,0, K_SPHERE | OP_END (0x400)}                   the last op: the walk returns
+  //   planar records: {n.xyz,d} {q.xyz,w.x} {v.xyz,w.y} {u.xyz,w.z}, or with linear_axis {n.xyz,d} {q.xyz,w.k} {S_alpha,0} {S_beta,0}
   const float4 *program;
-  uint32_t program_ops;         // 0: the scene has no program (too big, or wrappers nested in a way only the stack walk mirrors)
+  uint32_t program_ops;         // ops of the image, the end op included; 0: the scene has no program (too big, or wrappers nested in a way only the stack walk mirrors)
+  uint32_t linear_float4s;      // size of the image in float4 (ops + records)
+  uint32_t linear_axis;         // 1: every planar op is an axis-aligned quad and the image holds the reduced records (rt_pack.cpp axis_aligned_words)
   uint32_t stack_entries;       // traversal stack entries per thread this scene's walk can need (<= STACK_CAPACITY)
   // own BVH over world-space primitives (RT_TRAVERSAL_FAST): 4 x float4 per node
   //   n0 = {c0.x0, c0.x1, c0.y0, c0.y1}  n1 = {c1.x0, c1.x1, c1.y0, c1.y1}
@@ -86,9 +93,6 @@ struct Scene {
   // primitives
   const float4 *spheres;        // 2 per sphere: {cx,cy,cz,r} {mx,my,mz, flags (bit0: needs uv)}
   const float4 *planars;        // 4 per quad/triangle: {n.xyz,d} {q.xyz,w.x} {v.xyz,w.y} {u.xyz,w.z}
-  // linear program whose planar ops are all axis-aligned quads: {n.xyz,d} {q.xyz,w.k} {S_alpha.xyz,0} {S_beta.xyz,0}
-  // (rt_pack.cpp axis_aligned_words; read by the axis variant of trace_linear only), nullptr otherwise
-  const float4 *planars_axis;
   uint32_t sphere_count, planar_count;
   uint32_t flat_triangles;      // trace_flat (tiny scenes, kernel mode 5): bit i set = planar i is a triangle
   // second primitive set for flattened instances (FAST mode on scenes with wrappers) lives in the same arrays
@@ -105,7 +109,7 @@ struct Scene {
 // packer only keeps a program whose staging area fits (256 ops of 32 B + their primitives: 24 KB at most)
 constexpr uint32_t LINEAR_SMEM_MAX_BYTES = 24576;
 RTD_HD uint32_t linear_stage_bytes(uint32_t program_ops, uint32_t planar_count, uint32_t sphere_count) {
-  return 32u * program_ops + 64u * planar_count + 32u * sphere_count;
+  return 32u * (program_ops + 1u) + 64u * planar_count + 32u * sphere_count;      // + the end op
 }
 
 constexpr int MAX_CHUNK_TABLE = 32;

@@ -76,7 +76,7 @@ __device__ __forceinline__ void st_volatile_u32(uint32_t *p, uint32_t v) { *rein
 // staged in shared memory when they fit, and the walk reads them with generic loads (measured, r2i_linear_program_in_smem.jsonl:
 // Cornell box s1024 309.6 -> 306.1 ms, s128 42.6 -> 41.6 ms, scene 0 1.100 -> 1.071 ms; RT_LINEAR_SMEM=0 builds the global-memory walk)
 __host__ __device__ inline uint32_t linear_smem_bytes(const Scene &sc) {
-  return (RT_LINEAR_SMEM && sc.program_ops > 0) ? rtd::linear_stage_bytes(sc.program_ops, sc.planar_count, sc.sphere_count) : 0u;
+  return (RT_LINEAR_SMEM && sc.program_ops > 0) ? 16u * sc.linear_float4s : 0u;
 }
 
 template <int MODE, bool AX, class C>
@@ -103,28 +103,23 @@ __device__ __forceinline__ size_t image_pixel(const RenderArgs &a, int pix) {
   return (size_t)image_row(a, y) * (size_t)a.img_width + (size_t)(pix - y * a.img_width);
 }
 
-// AX (kernel modes 3 / 4 only): every planar op of the program is an axis-aligned quad; the walk reads Scene::planars_axis
-// and runs the reduced inside test (planar_inside_axis in rt_trace.cuh) -- same roundings, fewer instructions, no triangle case
+// AX (kernel modes 3 / 4 only): every planar op of the program is an axis-aligned quad; the program's image holds the reduced
+// records and the walk runs the reduced inside test (planar_inside_axis in rt_trace.cuh) -- same roundings, fewer
+// instructions, no triangle case
 template <int MODE, int MAXB, bool COUNT, bool AX = false>
 __global__ void __launch_bounds__(RT_BLOCK, min_blocks(MODE)) render_kernel(const RenderArgs a) {
   extern __shared__ __align__(16) uint32_t smem[];
-#if RT_LINEAR_SMEM
   Scene sc = a.scene;
-  if (AX) sc.planars = a.scene.planars_axis;
-  // unconditional (the packer keeps a program only if this fits): the walk's pointers are then shared-memory pointers at
-  // compile time, and its loads LDS with an immediate offset instead of generic loads behind a 64-bit address computation
+#if RT_LINEAR_SMEM
+  // The image of the linear program (ops + the records they test, one block; the packer keeps a program only if it fits) is
+  // copied to shared memory unconditionally: the walk's pointer is then a shared-memory pointer at compile time (LDS with
+  // immediate offsets), and everything it reads is addressed relative to the op at hand -- no base address inside the walk.
   if (MODE == 3 || MODE == 4) {                                              // the staging area is the last part of smem
     float4 *dst = reinterpret_cast<float4 *>(smem + a.linear_smem_word);
-    const uint32_t n_prog = 2u * sc.program_ops, n_plan = 4u * sc.planar_count, n_sph = 2u * sc.sphere_count;
-    for (uint32_t i = threadIdx.x; i < n_prog; i += blockDim.x) dst[i] = __ldg(a.scene.program + i);
-    for (uint32_t i = threadIdx.x; i < n_plan; i += blockDim.x) dst[n_prog + i] = __ldg((AX ? a.scene.planars_axis : a.scene.planars) + i);
-    for (uint32_t i = threadIdx.x; i < n_sph; i += blockDim.x) dst[n_prog + n_plan + i] = __ldg(a.scene.spheres + i);
-    sc.program = dst; sc.planars = dst + n_prog; sc.spheres = dst + n_prog + n_plan;
+    for (uint32_t i = threadIdx.x; i < sc.linear_float4s; i += blockDim.x) dst[i] = __ldg(a.scene.program + i);
+    sc.program = dst;
     __syncthreads();
   }
-#else
-  Scene sc = a.scene;
-  if (AX) sc.planars = a.scene.planars_axis;
 #endif
   uint32_t *stk = smem + threadIdx.x;
   constexpr int stride = RT_BLOCK;                       // launch_render_t always launches RT_BLOCK threads
@@ -497,9 +492,8 @@ __global__ void __launch_bounds__(PROBE_BLOCK) probe_trace_kernel(const Scene sc
   rtt::NoCount cnt;
   if (MODE == 0) hit = rtt::trace_reference<true>(sc, r, tmin, tmax, h, smem + threadIdx.x, blockDim.x, cnt);
   else if (MODE == 3) {
-    if (sc.planars_axis != nullptr) {                      // the walk the render kernel runs on this scene (AX)
-      Scene ax = sc; ax.planars = sc.planars_axis;
-      hit = rtt::trace_linear<false, true>(ax, r, tmin, tmax, h, cnt);
+    if (sc.linear_axis) {                                  // the walk the render kernel runs on this scene (AX)
+      hit = rtt::trace_linear<false, true>(sc, r, tmin, tmax, h, cnt);
     } else {
       hit = rtt::trace_linear(sc, r, tmin, tmax, h, cnt);
     }
@@ -637,7 +631,7 @@ cudaError_t launch_render(const rtd::RenderArgs &args, int mode, int sm_count, c
     if (mode >= 3) return launch_render_t<3, 256, true>(args, sm_count, stream, info);
     return launch_render_t<1, 256, true>(args, sm_count, stream, info);
   }
-  if (args.scene.planars_axis != nullptr && (mode == 3 || mode == 4)) {   // linear program of axis-aligned quads (see render_kernel, AX)
+  if (args.scene.linear_axis && (mode == 3 || mode == 4)) {   // linear program of axis-aligned quads (see render_kernel, AX)
     if (args.forward) return mode == 4 ? launch_render_t<4, 0, false, true>(args, sm_count, stream, info) : launch_render_t<3, 0, false, true>(args, sm_count, stream, info);
     if (mode == 4 && small) return launch_render_t<4, 64, false, true>(args, sm_count, stream, info);
     return small ? launch_render_t<3, 64, false, true>(args, sm_count, stream, info) : launch_render_t<3, 256, false, true>(args, sm_count, stream, info);

@@ -706,6 +706,42 @@ struct Packer {
 
 }  // namespace
 
+void build_linear_image(const PackedScene &p, bool axis, std::vector<float4> &image) {
+  image.clear();
+  if (p.program.empty()) return;
+  const size_t n = p.program.size() / 2, n1 = n + 1;
+  const std::vector<float4> &planars = (axis && p.program_axis_quads) ? p.planars_axis : p.planars;
+  image.reserve(2 * n1 + planars.size() + p.spheres.size());
+  image.assign(p.program.begin(), p.program.end());
+  for (size_t i = 0; i < n; ++i) {
+    float4 &w1 = image[2 * i + 1];
+    uint32_t code, arg;
+    memcpy(&code, &w1.w, 4); memcpy(&arg, &w1.z, 4);
+    int32_t delta;
+    switch (code & 7u) {
+      case K_BVH:                                          // skip target: op index -> bytes from this op
+        delta = ((int32_t)arg - (int32_t)i) * 32;
+        memcpy(&w1.z, &delta, 4);
+        break;
+      case K_TRIANGLE: case K_QUAD:
+        delta = (int32_t)((n1 - i) * 32 + 64 * (size_t)arg);
+        memcpy(&w1.x, &delta, 4);
+        break;
+      case K_SPHERE:
+        delta = (int32_t)((n1 - i) * 32 + 16 * planars.size() + 32 * (size_t)arg);
+        memcpy(&w1.x, &delta, 4);
+        break;
+      default: break;
+    }
+  }
+  const uint32_t end_code = K_SPHERE | 0x400u;
+  float4 e0 = {0, 0, 0, 0}, e1 = {0, 0, 0, 0};
+  memcpy(&e1.w, &end_code, 4);
+  image.push_back(e0); image.push_back(e1);
+  image.insert(image.end(), planars.begin(), planars.end());
+  image.insert(image.end(), p.spheres.begin(), p.spheres.end());
+}
+
 int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out, uint32_t treelet_min, uint32_t fuse_min,
                uint32_t program_max) {
   if (traversal > RT_TRAVERSAL_FAST) { out.error = "rt_scene_upload: unknown traversal mode"; return RT_ERR_INVALID; }

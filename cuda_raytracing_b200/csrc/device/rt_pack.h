@@ -50,6 +50,10 @@ constexpr uint32_t PROGRAM_MAX_DEFAULT = 256;
 int pack_scene(const rt_scene_desc &desc, uint32_t traversal, PackedScene &out, uint32_t treelet_min = 8,
                uint32_t fuse_min = 8, uint32_t program_max = PROGRAM_MAX_DEFAULT);
 
+// the image of the linear program the kernels walk (rt_device.h, Scene::program): p.program with its indices turned into
+// byte offsets relative to the op, the end op, then the planar records (the reduced ones with `axis`) and the sphere records
+void build_linear_image(const PackedScene &p, bool axis, std::vector<float4> &image);
+
 // one reference Material (24 B) -> the two 16-byte words of a device material record, pre-resolving its
 // texture against `arena`; may append to out.checkers / perlin tables.
 void pack_material(const rt_material &m, const uint8_t *arena, uint64_t arena_bytes, PackedScene &out, uint4 rec[2]);

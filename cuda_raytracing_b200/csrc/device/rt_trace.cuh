@@ -54,11 +54,11 @@ struct OpCount {
 // ---- sphere (rt.cu:1093-1123): a = d.d is passed in (it only changes when a wrapper rotates the ray) ----
 // The test (which root, if any, lies in (tmin,tmax)) and the hit record are separate so that the warp-scheduled
 // kernel can carry only (t, prim) through a traversal and build the record once, for the closest hit.
+// `rec` = the sphere's two words, wherever they are (Scene::spheres, or the image of a linear program)
 template <bool G = false>
-__device__ __forceinline__ bool sphere_root(const Scene &sc, uint32_t idx, const Ray &r, float a, float tmin, float tmax,
-                                            float &root_out) {
-  const float4 s0 = ldx<G>(sc.spheres + 2 * idx);
-  const float4 s1 = ldx<G>(sc.spheres + 2 * idx + 1);
+__device__ __forceinline__ bool sphere_root_rec(const float4 *rec, const Ray &r, float a, float tmin, float tmax, float &root_out) {
+  const float4 s0 = ldx<G>(rec);
+  const float4 s1 = ldx<G>(rec + 1);
   const V3 c = v3(ffma(r.time, s1.x, s0.x), ffma(r.time, s1.y, s0.y), ffma(r.time, s1.z, s0.z));   // movement_path_at
   const V3 oc = vsub(c, r.o);
   const float b = fmul(dot_yfirst(r.d, oc), -2.0f);
@@ -74,9 +74,14 @@ __device__ __forceinline__ bool sphere_root(const Scene &sc, uint32_t idx, const
   return true;
 }
 template <bool G = false>
-__device__ __forceinline__ void sphere_record(const Scene &sc, uint32_t idx, const Ray &r, float root, Hit &h) {
-  const float4 s0 = ldx<G>(sc.spheres + 2 * idx);
-  const float4 s1 = ldx<G>(sc.spheres + 2 * idx + 1);
+__device__ __forceinline__ bool sphere_root(const Scene &sc, uint32_t idx, const Ray &r, float a, float tmin, float tmax,
+                                            float &root_out) {
+  return sphere_root_rec<G>(sc.spheres + 2 * idx, r, a, tmin, tmax, root_out);
+}
+template <bool G = false>
+__device__ __forceinline__ void sphere_record_rec(const float4 *rec, uint32_t idx, const Ray &r, float root, Hit &h) {
+  const float4 s0 = ldx<G>(rec);
+  const float4 s1 = ldx<G>(rec + 1);
   const V3 c = v3(ffma(r.time, s1.x, s0.x), ffma(r.time, s1.y, s0.y), ffma(r.time, s1.z, s0.z));
   h.t = root;
   h.p = along(r.o, root, r.d);
@@ -95,13 +100,21 @@ __device__ __forceinline__ void sphere_record(const Scene &sc, uint32_t idx, con
   h.prim = idx;
 }
 template <bool G = false>
-__device__ __forceinline__ bool hit_sphere(const Scene &sc, uint32_t idx, const Ray &r, float a, float tmin, float &tmax,
-                                           Hit &h) {
+__device__ __forceinline__ void sphere_record(const Scene &sc, uint32_t idx, const Ray &r, float root, Hit &h) {
+  sphere_record_rec<G>(sc.spheres + 2 * idx, idx, r, root, h);
+}
+template <bool G = false>
+__device__ __forceinline__ bool hit_sphere_rec(const float4 *rec, uint32_t idx, const Ray &r, float a, float tmin, float &tmax, Hit &h) {
   float root;
-  if (!sphere_root<G>(sc, idx, r, a, tmin, tmax, root)) return false;
-  sphere_record<G>(sc, idx, r, root, h);
+  if (!sphere_root_rec<G>(rec, r, a, tmin, tmax, root)) return false;
+  sphere_record_rec<G>(rec, idx, r, root, h);
   tmax = root;
   return true;
+}
+template <bool G = false>
+__device__ __forceinline__ bool hit_sphere(const Scene &sc, uint32_t idx, const Ray &r, float a, float tmin, float &tmax,
+                                           Hit &h) {
+  return hit_sphere_rec<G>(sc.spheres + 2 * idx, idx, r, a, tmin, tmax, h);
 }
 
 // ---- quad / triangle (rt.cu:1131-1175 with geom_calc_hit 1060-1077) ----
@@ -120,23 +133,23 @@ __device__ __forceinline__ bool planar_inside_rec(const float4 p1, const float4 
   if (triangle) inside = inside && (fadd(alpha, beta) <= 1.0f);
   return inside;
 }
+// `rec` = the four words of the record, wherever they are (Scene::planars, or the image of a linear program)
 template <bool G = false>
-__device__ __forceinline__ bool planar_inside(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float t, V3 &p,
-                                              float &alpha, float &beta) {
-  const float4 p1 = ldx<G>(sc.planars + 4 * idx + 1);      // q, w.x
-  const float4 p2 = ldx<G>(sc.planars + 4 * idx + 2);      // v, w.y
-  const float4 p3 = ldx<G>(sc.planars + 4 * idx + 3);      // u, w.z
+__device__ __forceinline__ bool planar_inside(const float4 *rec, bool triangle, const Ray &r, float t, V3 &p, float &alpha, float &beta) {
+  const float4 p1 = ldx<G>(rec + 1);                       // q, w.x
+  const float4 p2 = ldx<G>(rec + 2);                       // v, w.y
+  const float4 p3 = ldx<G>(rec + 3);                       // u, w.z
   return planar_inside_rec(p1, p2, p3, triangle, r, t, p, alpha, beta);
 }
-// Axis-aligned quad (Scene::planars_axis, words {q, w.k} {S_alpha} {S_beta}; rt_pack.cpp axis_aligned_words has the
+// Axis-aligned quad (reduced record {n,d} {q, w.k} {S_alpha} {S_beta}; rt_pack.cpp axis_aligned_words has the
 // derivation): with one non-zero component in each of w, u, v the reference's two cross products and dot products reduce,
 // rounding for rounding, to alpha = fl(w.k * fl(pl.m * s)) -- fl(pl.m * s) evaluated as dot(pl, S), S zero except s at m,
-// so that no component has to be picked at run time.  18 instead of 30 operations for the two coordinates.
+// so that no component has to be picked at run time.  8 instead of 18 operations for the two coordinates.
 template <bool G = false>
-__device__ __forceinline__ bool planar_inside_axis(const Scene &sc, uint32_t idx, const Ray &r, float t, V3 &p, float &alpha, float &beta) {
-  const float4 p1 = ldx<G>(sc.planars + 4 * idx + 1);      // q, w.k
-  const float4 p2 = ldx<G>(sc.planars + 4 * idx + 2);      // S_alpha
-  const float4 p3 = ldx<G>(sc.planars + 4 * idx + 3);      // S_beta
+__device__ __forceinline__ bool planar_inside_axis(const float4 *rec, const Ray &r, float t, V3 &p, float &alpha, float &beta) {
+  const float4 p1 = ldx<G>(rec + 1);                       // q, w.k
+  const float4 p2 = ldx<G>(rec + 2);                       // S_alpha
+  const float4 p3 = ldx<G>(rec + 3);                       // S_beta
   p = along(r.o, t, r.d);
   const V3 pl = vsub(p, v3(p1.x, p1.y, p1.z));
   alpha = fmul(p1.w, dot_yfirst(pl, v3(p2.x, p2.y, p2.z)));
@@ -145,10 +158,10 @@ __device__ __forceinline__ bool planar_inside_axis(const Scene &sc, uint32_t idx
 }
 // `p0` = first word of the record (normal, d): the linear program carries it inside the op, the other walks load it here
 template <bool EAGER = false, bool G = false, bool AX = false>
-__device__ __forceinline__ bool planar_t_p0(const Scene &sc, const float4 p0, uint32_t idx, bool triangle, const Ray &r, float tmin,
-                                            float tmax, float &t_out) {
+__device__ __forceinline__ bool planar_t_p0(const float4 *rec, const float4 p0, bool triangle, const Ray &r, float tmin, float tmax,
+                                            float &t_out) {
   float4 p1 = p0, p2 = p0, p3 = p0;
-  if (EAGER) { p1 = ldg4(sc.planars + 4 * idx + 1); p2 = ldg4(sc.planars + 4 * idx + 2); p3 = ldg4(sc.planars + 4 * idx + 3); }
+  if (EAGER) { p1 = ldg4(rec + 1); p2 = ldg4(rec + 2); p3 = ldg4(rec + 3); }
   const V3 n = v3(p0.x, p0.y, p0.z);
   const float denom = dot_yfirst(n, r.d);
   // reference: fabsf(denom) >= 1e-8 evaluated in double; (float)1e-8 < 1e-8, so in f32 this is a strict '>'
@@ -163,30 +176,31 @@ __device__ __forceinline__ bool planar_t_p0(const Scene &sc, const float4 p0, ui
   const float t = zero_num ? __uint_as_float((__float_as_uint(num) ^ __float_as_uint(denom)) & 0x80000000u) : quot;
   if (!(tmin <= t && t <= tmax)) return false;
   V3 p; float alpha, beta;
-  if (AX) { if (!planar_inside_axis<G>(sc, idx, r, t, p, alpha, beta)) return false; }
-  else if (EAGER ? !planar_inside_rec(p1, p2, p3, triangle, r, t, p, alpha, beta) : !planar_inside<G>(sc, idx, triangle, r, t, p, alpha, beta)) return false;
+  if (AX) { if (!planar_inside_axis<G>(rec, r, t, p, alpha, beta)) return false; }
+  else if (EAGER ? !planar_inside_rec(p1, p2, p3, triangle, r, t, p, alpha, beta) : !planar_inside<G>(rec, triangle, r, t, p, alpha, beta)) return false;
   t_out = t;
   return true;
 }
 template <bool EAGER = false>
 __device__ __forceinline__ bool planar_t(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float tmin, float tmax,
                                          float &t_out) {
-  return planar_t_p0<EAGER>(sc, ldg4(sc.planars + 4 * idx), idx, triangle, r, tmin, tmax, t_out);
+  return planar_t_p0<EAGER>(sc.planars + 4 * idx, ldg4(sc.planars + 4 * idx), triangle, r, tmin, tmax, t_out);
 }
+// `prim` = the primitive id of the planar (sphere_count + its index)
 template <bool G = false, bool AX = false>
-__device__ __forceinline__ void planar_record_p0(const Scene &sc, const float4 p0, uint32_t idx, const Ray &r, float t, Hit &h) {
+__device__ __forceinline__ void planar_record_p0(const float4 *rec, const float4 p0, uint32_t prim, const Ray &r, float t, Hit &h) {
   const V3 n = v3(p0.x, p0.y, p0.z);
   const float denom = dot_yfirst(n, r.d);
   float alpha, beta;
-  if (AX) planar_inside_axis<G>(sc, idx, r, t, h.p, alpha, beta);
-  else planar_inside<G>(sc, idx, false, r, t, h.p, alpha, beta);
+  if (AX) planar_inside_axis<G>(rec, r, t, h.p, alpha, beta);
+  else planar_inside<G>(rec, false, r, t, h.p, alpha, beta);
   h.u = alpha; h.v = beta; h.t = t;
   h.front = denom < 0.0f;
   h.n = h.front ? n : vneg(n);
-  h.prim = sc.sphere_count + idx;
+  h.prim = prim;
 }
 __device__ __forceinline__ void planar_record(const Scene &sc, uint32_t idx, const Ray &r, float t, Hit &h) {
-  planar_record_p0(sc, ldg4(sc.planars + 4 * idx), idx, r, t, h);
+  planar_record_p0(sc.planars + 4 * idx, ldg4(sc.planars + 4 * idx), sc.sphere_count + idx, r, t, h);
 }
 template <bool EAGER = false>
 __device__ __forceinline__ bool hit_planar(const Scene &sc, uint32_t idx, bool triangle, const Ray &r, float tmin, float &tmax,
@@ -198,11 +212,11 @@ __device__ __forceinline__ bool hit_planar(const Scene &sc, uint32_t idx, bool t
   return true;
 }
 template <bool EAGER = false, bool G = false, bool AX = false>
-__device__ __forceinline__ bool hit_planar_p0(const Scene &sc, const float4 p0, uint32_t idx, bool triangle, const Ray &r, float tmin,
+__device__ __forceinline__ bool hit_planar_p0(const float4 *rec, const float4 p0, uint32_t prim, bool triangle, const Ray &r, float tmin,
                                               float &tmax, Hit &h) {
   float t;
-  if (!planar_t_p0<EAGER, G, AX>(sc, p0, idx, triangle, r, tmin, tmax, t)) return false;
-  planar_record_p0<G, AX>(sc, p0, idx, r, t, h);
+  if (!planar_t_p0<EAGER, G, AX>(rec, p0, triangle, r, tmin, tmax, t)) return false;
+  planar_record_p0<G, AX>(rec, p0, prim, r, t, h);
   tmax = t;
   return true;
 }
@@ -458,37 +472,45 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
 // A variant that walked the program in lockstep (every step the lowest op any lane has to do, redux.sync min; each op
 // issued once per warp and ray) ran 14 % SLOWER than the stack walk: 7 % fewer warp-instructions, but every step a
 // serial chain vote -> op load -> branch -> test, and the lanes' inside tests no longer overlap across quads.
-constexpr uint32_t OP_T_EXIT = 6u, OP_R_EXIT = 7u, OP_IN_WRAPPER = 0x100u, OP_FUSED_WRAPPER = 0x200u;
+constexpr uint32_t OP_T_EXIT = 6u, OP_R_EXIT = 7u, OP_IN_WRAPPER = 0x100u, OP_FUSED_WRAPPER = 0x200u, OP_END = 0x400u;
 template <bool G = false, bool AX = false, class C>
 __device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin, float tmax, Hit &h, C &cnt) {
   bool result = false, was_last_hit = false;
   V3 inv = v3(frcp(r.d.x), frcp(r.d.y), frcp(r.d.z));
   float a = dot_xfirst(r.d, r.d);
-  // the walk keeps the ADDRESS of its next op (in the kernels of modes 3 / 4 a 32-bit shared-memory address: two LDS.128 with
-  // immediate offsets and one add per step, no index arithmetic)
+  // The walk keeps the ADDRESS of its next op (in the kernels of modes 3 / 4 a 32-bit shared-memory address) and reaches
+  // everything else -- a primitive's record, the op after a missed box -- by a byte offset from the op at hand that the op
+  // itself carries (rt_device.h, Scene::program): two LDS.128 with immediate offsets and one add per step, no base address
+  // and no bound to recompute (with both, ptxas rebuilt the shared window's address from special registers at every use:
+  // 10.8 % of the warp-instructions of the Cornell box).  The last op of every program is the end op.
   const float4 *op = sc.program;
-  const float4 *const end = sc.program + 2 * sc.program_ops;
-  while (op < end) {
+  for (;;) {
+    const float4 *const self = op;
     const float4 w0 = ldx<G>(op), w1 = ldx<G>(op + 1);
     const uint32_t code = __float_as_uint(w1.w), arg = __float_as_uint(w1.z);
     op += 2;
     switch (code & 7u) {
-      case rtd::K_SPHERE:
+      case rtd::K_SPHERE: {
+        if (code & OP_END) return result;
+        const float4 *rec = reinterpret_cast<const float4 *>(reinterpret_cast<const char *>(self) + __float_as_int(w1.x));
         cnt.sphere();
-        if (hit_sphere<G>(sc, arg, r, a, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
-        break;
+        if (hit_sphere_rec<G>(rec, arg, r, a, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
+      } break;
       case rtd::K_TRIANGLE:
-      case rtd::K_QUAD:
+      case rtd::K_QUAD: {
+        const float4 *rec = reinterpret_cast<const float4 *>(reinterpret_cast<const char *>(self) + __float_as_int(w1.x));
         cnt.planar();
-        if (hit_planar_p0<false, G, AX>(sc, w0, arg, !AX && (code & 7u) == rtd::K_TRIANGLE, r, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
-        break;
+        if (hit_planar_p0<false, G, AX>(rec, w0, sc.sphere_count + arg, !AX && (code & 7u) == rtd::K_TRIANGLE, r, tmin, tmax, h)) {
+          result = true; if (code & OP_IN_WRAPPER) was_last_hit = true;
+        }
+      } break;
       case rtd::K_BVH: {
         float t0 = tmin, t1 = tmax;
         cnt.box(1);
         const bool ax = aabb_axis(w0.x, w0.y, r.o.x, inv.x, t0, t1);
         const bool ay = aabb_axis(w0.z, w0.w, r.o.y, inv.y, t0, t1);
         const bool az = aabb_axis(w1.x, w1.y, r.o.z, inv.z, t0, t1);
-        if (!(ax & ay & az)) op = sc.program + 2 * arg;
+        if (!(ax & ay & az)) op = reinterpret_cast<const float4 *>(reinterpret_cast<const char *>(self) + (int)arg);
       } break;
       case rtd::K_TRANSLATION:
         cnt.translation();

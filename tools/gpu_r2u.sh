@@ -1,5 +1,5 @@
 #!/usr/bin/env bash
-# Round 2, GPU call U (second run): linear walk keeps the address of its next op; before: C4 279.5-283, C4s 38.27, C4t 20.64, C1 0.977 ms
+# Round 2, GPU call U (third run): linear walk addressed relative to the op at hand, end op instead of a bound; before: C4 279.0-279.6, C4s 38.06-38.25, C4t 20.63, C1 0.944-0.962 ms, general inside test 297.5
 set -u
 mkdir -p gpurun_out
 K="python tools/gpu_knobs.py"
