@@ -635,7 +635,7 @@ struct Packer {
     }
     const uint32_t root_href = d.world_refs[d.root_wref];
     out.ref_root = tag[root_href];
-    out.ref_stack_need = stack_need(root_href, 0, 0) + 1;
+    out.ref_stack_need = stack_need(root_href, 0, 0) + 2;        // + the root, + the bottom sentinel (rt_trace.cuh)
     // small scenes with wrappers (where neither treelets nor fused instances were worth planting): the same walk as a
     // linear program.  RT_TRAVERSAL_REFERENCE stays the literal stack walk (the mode to bisect against).
     if (traversal == RT_TRAVERSAL_AUTO && !want_fast && program_max > 0 && out.treelets + out.fused_instances == 0 &&
@@ -666,12 +666,12 @@ struct Packer {
         out.fast_nodes[2] = f4(b.lo[2], b.hi[2], INFINITY, -INFINITY);
         out.fast_nodes[3] = f4(as_float(leaves[0].ref), as_float(make_ref(K_NONE, 0)), 0.0f, 0.0f);
         out.fast_root = make_ref(K_BVH, 0);
-        out.fast_stack_need = 2;
+        out.fast_stack_need = 3;
       } else {
         SahBuilder sb(leaves, out.fast_nodes);
         Box rb;
         out.fast_root = sb.build(0, leaves.size(), 0, rb);
-        out.fast_stack_need = sb.max_depth + 2;
+        out.fast_stack_need = sb.max_depth + 3;               // + the bottom sentinel
       }
       out.has_fast = true;
     }

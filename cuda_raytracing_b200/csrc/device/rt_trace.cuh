@@ -10,14 +10,19 @@
 
 // a push onto the per-thread traversal stack; -DRT_STACK_CHECK builds trap when a walk needs more entries than the packer
 // computed for the scene (tools/build_variants.sh stackcheck "-DRT_STACK_CHECK", then the GPU tests with RT_B200_LIB)
+// The stack is walked by ADDRESS (`top`), not by index: a push is one store and one add, a pop one add and one load, and the
+// bottom is a sentinel entry instead of a compare against the base -- with an index ptxas rebuilt the shared window's base
+// from special registers at every push and pop (3 % of the warp-instructions of C2 and C5).
 #ifdef RT_STACK_CHECK
-#define RT_PUSH(v) do { if (sp >= (int)sc.stack_entries) __trap(); stk[(sp++) * stride] = (v); } while (0)
+#define RT_PUSH(v) do { if (top >= stk + (size_t)sc.stack_entries * stride) __trap(); *top = (v); top += stride; } while (0)
 #else
-#define RT_PUSH(v) (stk[(sp++) * stride] = (v))
+#define RT_PUSH(v) (*top = (v), top += stride)
 #endif
+#define RT_POP() (top -= stride, *top)
 
 namespace rtt {
 using namespace rtm;
+constexpr uint32_t STACK_BOTTOM = 0xffffffffu;             // no link looks like this (kind K_NONE, instance bit, index 2^28 - 1)
 using rtd::Scene;
 
 struct Ray { V3 o, d; float time; };
@@ -272,8 +277,9 @@ template <bool TREELETS, class C>
 __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float tmin, float tmax, Hit &h,
                                                 uint32_t *stk, const int stride, C &cnt) {
   bool result = false, was_last_hit = false, in_translation = false, in_rotation = false;
-  int sp = 0;
-  stk[0] = sc.ref_root; sp = 1;
+  uint32_t *top = stk;
+  RT_PUSH(STACK_BOTTOM);
+  RT_PUSH(sc.ref_root);
   V3 inv = v3(frcp(r.d.x), frcp(r.d.y), frcp(r.d.z));
   float a = dot_xfirst(r.d, r.d);
   // slab constants of the own nodes (see slab_pair); recomputed after a wrapper moved the ray
@@ -281,8 +287,9 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
   V3 cinv = inv, noi = inv;
   float slack = 0.0f;
   // every item goes through the stack and is popped here: one place where the lanes of a warp meet again
-  while (sp > 0) {
-    const uint32_t cur = stk[(--sp) * stride];
+  for (;;) {
+    const uint32_t cur = RT_POP();
+    if (cur == STACK_BOTTOM) break;
     const uint32_t idx = rtd::ref_index(cur);
     switch (rtd::ref_kind(cur)) {
       case rtd::K_SPHERE:
@@ -675,7 +682,8 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
   const V3 inv = v3(fminf(fmaxf(frcp(r.d.x), -big), big), fminf(fmaxf(frcp(r.d.y), -big), big), fminf(fmaxf(frcp(r.d.z), -big), big));
   const V3 noi = v3(-(r.o.x * inv.x), -(r.o.y * inv.y), -(r.o.z * inv.z));
   const float slack = fminf((fabsf(noi.x) + fabsf(noi.y) + fabsf(noi.z)) * 4.76837158e-7f, 3.0e38f);
-  int sp = 0;
+  uint32_t *top = stk;
+  RT_PUSH(STACK_BOTTOM);
   uint32_t cur = sc.fast_root;
   for (;;) {
     const uint32_t kind = rtd::ref_kind(cur);
@@ -718,8 +726,8 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
       else { cnt.planar(); hit_in = planar_t(sc, ci, ck == rtd::K_TRIANGLE, q, tmin, tmax, tt); }
       if (hit_in) { tmax = tt; best = cur; }
     }                                                     // K_NONE: the empty second child of a one-primitive scene
-    if (sp == 0) break;
-    cur = stk[(--sp) * stride];
+    cur = RT_POP();
+    if (cur == STACK_BOTTOM) break;
   }
   if (best == 0xffffffffu) return false;
   if (rtd::ref_kind(best) == rtd::K_SPHERE) sphere_record(sc, rtd::ref_index(best), r, tmax, h);
