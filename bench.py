@@ -170,7 +170,7 @@ def run_reference_arm(args):
             "config": {"workload": WORKLOAD, "sample": "s%d of s%d per step" % (spp, SPP)},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -435,13 +435,32 @@ def run_gpu_arm(args):
         line["reference_gpu"] = {"kernel_ms": c4.get("reference_gpu_ms"),
                                  "value": (n * SPP / (c4["reference_gpu_ms"] / 1e3)) if c4.get("reference_gpu_ms") else None, "unit": UNIT,
                                  "what": "oracle/_ref/raytracing_ref (unmodified reference, nvcc -arch sm_100 -O3), its own 'Rendering time', same GPU, same run"}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.barrier(); dist.destroy_process_group()
     return 0
 
 
+def claim_stdout():
+    """stdout carries ONE JSON line.  Anything a library prints to fd 1 (NCCL's version line at NCCL_DEBUG=VERSION, for one)
+    goes to stderr instead: fd 1 is pointed at fd 2 for the whole run and the line is written to the saved descriptor."""
+    sys.stdout.flush()
+    real = os.dup(1)
+    os.dup2(2, 1)
+    return os.fdopen(real, "w")
+
+
+OUT = None
+
+
+def emit(line):
+    (OUT or sys.stdout).write(json.dumps(line) + "\n")
+    (OUT or sys.stdout).flush()
+
+
 def main():
+    global OUT
+    OUT = claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)

@@ -10,6 +10,7 @@
  * equal image), 'q' JSON stats line on stderr.
  */
 #include <stdio.h>
+#include <unistd.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -42,7 +43,19 @@ int main(int argc, char *argv[]) {
 
   rt_context *ctx = NULL;
   rt_group *group = NULL;
-  int rc = gpus > 1 ? rt_group_create(NULL, gpus, &group) : rt_context_create(0, &ctx);
+  /* stdout is the reference's four lines (scripts scrape them).  NCCL prints its version line to stdout at NCCL_DEBUG=VERSION
+   * whatever NCCL_DEBUG_FILE says, so while the group sets up its communicators fd 1 points at stderr. */
+  int rc;
+  if (gpus > 1) {
+    fflush(stdout);
+    const int saved = dup(1);
+    if (saved >= 0) dup2(2, 1);
+    rc = rt_group_create(NULL, gpus, &group);
+    fflush(stdout);
+    if (saved >= 0) { dup2(saved, 1); close(saved); }
+  } else {
+    rc = rt_context_create(0, &ctx);
+  }
   if (rc != RT_OK) { fprintf(stderr, "raytracing: %s\n", rt_last_error_string(NULL)); return 2; }
   rt_camera cam;
   rt_camera_setup(&settings, &cam);
