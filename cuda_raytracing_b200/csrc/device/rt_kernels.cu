@@ -628,7 +628,8 @@ cudaError_t launch_render(const rtd::RenderArgs &args, int mode, int sm_count, c
     if (mode == 2) return launch_render_t<2, 256, true>(args, sm_count, stream, info);
     if (mode == 5) return launch_render_t<5, 256, true>(args, sm_count, stream, info);
     if (mode == 6) return launch_render_t<6, 256, true>(args, sm_count, stream, info);
-    if (mode >= 3) return launch_render_t<3, 256, true>(args, sm_count, stream, info);
+    if (mode >= 3) return args.scene.linear_axis ? launch_render_t<3, 256, true, true>(args, sm_count, stream, info)   // the image holds the reduced records
+                                                 : launch_render_t<3, 256, true>(args, sm_count, stream, info);
     return launch_render_t<1, 256, true>(args, sm_count, stream, info);
   }
   if (args.scene.linear_axis && (mode == 3 || mode == 4)) {   // linear program of axis-aligned quads (see render_kernel, AX)

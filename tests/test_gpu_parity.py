@@ -400,6 +400,21 @@ def test_image_does_not_depend_on_scheduling_knobs(product_lib, sid):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("sid", [1, 0, 2, 3, 17])
+def test_instrumented_kernel_renders_the_same_image(gpu_ctx, product_lib, sid):
+    """RT_RENDER_COUNT_OPS selects the instrumented build of the same walk (it feeds bench.py's roofline): same image, same
+    ray count as the timed kernel -- on scene 1 that is the build with the reduced inside test of axis-aligned quads."""
+    hs = product_lib.HostScene(sid)
+    gpu_ctx.upload(hs, product_lib.RT_TRAVERSAL_AUTO)
+    plain, _, st0 = gpu_ctx.render(hs.params(120, 12, 20, flags=product_lib.RT_RENDER_COUNT_RAYS))
+    counted, _, st1 = gpu_ctx.render(hs.params(120, 12, 20, flags=product_lib.RT_RENDER_COUNT_OPS))
+    assert np.array_equal(common.bits(counted), common.bits(plain))
+    assert st0.rays == st1.rays > 0
+    assert sum(st1.ops) > 0
+    hs.close()
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("sid", sorted(WRAPPER_SCENES))
 def test_hybrid_walk_equals_reference_order(product_lib, sid):
     """RT_TRAVERSAL_AUTO on scenes with instance wrappers: treelets (own BVH inside wrapper-free subtrees) and fused
