@@ -460,7 +460,6 @@ def emit(line):
 
 def main():
     global OUT
-    OUT = claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -469,6 +468,7 @@ def main():
     ap.add_argument("--no-reference-gpu", action="store_true", help="skip timing the reference's own CUDA binary")
     ap.add_argument("--no-configs", action="store_true", help="skip the per-config block (N=1)")
     args = ap.parse_args()
+    OUT = claim_stdout()
     if args.impl == "reference":
         return run_reference_arm(args)
     return run_gpu_arm(args)
