@@ -722,10 +722,14 @@ void build_linear_image(const PackedScene &p, bool axis, std::vector<float4> &im
       case K_BVH:                                          // skip target: op index -> bytes from this op
         delta = ((int32_t)arg - (int32_t)i) * 32;
         memcpy(&w1.z, &delta, 4);
+        code |= 0x10u;                                     // OP_IS_BOX (rt_trace.cuh): the two frequent kinds get a flag bit each
+        memcpy(&w1.w, &code, 4);
         break;
       case K_TRIANGLE: case K_QUAD:
         delta = (int32_t)((n1 - i) * 32 + 64 * (size_t)arg);
         memcpy(&w1.x, &delta, 4);
+        code |= 0x8u;                                      // OP_IS_PLANAR
+        memcpy(&w1.w, &code, 4);
         break;
       case K_SPHERE:
         delta = (int32_t)((n1 - i) * 32 + 16 * planars.size() + 32 * (size_t)arg);

@@ -479,7 +479,8 @@ __device__ __forceinline__ bool trace_reference(const Scene &sc, Ray &r, float t
 // A variant that walked the program in lockstep (every step the lowest op any lane has to do, redux.sync min; each op
 // issued once per warp and ray) ran 14 % SLOWER than the stack walk: 7 % fewer warp-instructions, but every step a
 // serial chain vote -> op load -> branch -> test, and the lanes' inside tests no longer overlap across quads.
-constexpr uint32_t OP_T_EXIT = 6u, OP_R_EXIT = 7u, OP_IN_WRAPPER = 0x100u, OP_FUSED_WRAPPER = 0x200u, OP_END = 0x400u;
+constexpr uint32_t OP_T_EXIT = 6u, OP_R_EXIT = 7u, OP_IN_WRAPPER = 0x100u, OP_FUSED_WRAPPER = 0x200u, OP_END = 0x400u,
+                   OP_IS_PLANAR = 0x8u, OP_IS_BOX = 0x10u;   // set in the image (build_linear_image) beside the kind
 template <bool G = false, bool AX = false, class C>
 __device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin, float tmax, Hit &h, C &cnt) {
   bool result = false, was_last_hit = false;
@@ -496,28 +497,31 @@ __device__ __forceinline__ bool trace_linear(const Scene &sc, Ray &r, float tmin
     const float4 w0 = ldx<G>(op), w1 = ldx<G>(op + 1);
     const uint32_t code = __float_as_uint(w1.w), arg = __float_as_uint(w1.z);
     op += 2;
+    // the two kinds that make up nine ops in ten carry a flag bit of their own in the image (one LOP3 into a predicate and a
+    // branch each; the switch over the kind was a chain of up to three compare-and-branch pairs in front of every op)
+    if (code & OP_IS_PLANAR) {
+      const float4 *rec = reinterpret_cast<const float4 *>(reinterpret_cast<const char *>(self) + __float_as_int(w1.x));
+      cnt.planar();
+      if (hit_planar_p0<false, G, AX>(rec, w0, sc.sphere_count + arg, !AX && (code & 7u) == rtd::K_TRIANGLE, r, tmin, tmax, h)) {
+        result = true; if (code & OP_IN_WRAPPER) was_last_hit = true;
+      }
+      continue;
+    }
+    if (code & OP_IS_BOX) {
+      float t0 = tmin, t1 = tmax;
+      cnt.box(1);
+      const bool ax = aabb_axis(w0.x, w0.y, r.o.x, inv.x, t0, t1);
+      const bool ay = aabb_axis(w0.z, w0.w, r.o.y, inv.y, t0, t1);
+      const bool az = aabb_axis(w1.x, w1.y, r.o.z, inv.z, t0, t1);
+      if (!(ax & ay & az)) op = reinterpret_cast<const float4 *>(reinterpret_cast<const char *>(self) + (int)arg);
+      continue;
+    }
     switch (code & 7u) {
       case rtd::K_SPHERE: {
         if (code & OP_END) return result;
         const float4 *rec = reinterpret_cast<const float4 *>(reinterpret_cast<const char *>(self) + __float_as_int(w1.x));
         cnt.sphere();
         if (hit_sphere_rec<G>(rec, arg, r, a, tmin, tmax, h)) { result = true; if (code & OP_IN_WRAPPER) was_last_hit = true; }
-      } break;
-      case rtd::K_TRIANGLE:
-      case rtd::K_QUAD: {
-        const float4 *rec = reinterpret_cast<const float4 *>(reinterpret_cast<const char *>(self) + __float_as_int(w1.x));
-        cnt.planar();
-        if (hit_planar_p0<false, G, AX>(rec, w0, sc.sphere_count + arg, !AX && (code & 7u) == rtd::K_TRIANGLE, r, tmin, tmax, h)) {
-          result = true; if (code & OP_IN_WRAPPER) was_last_hit = true;
-        }
-      } break;
-      case rtd::K_BVH: {
-        float t0 = tmin, t1 = tmax;
-        cnt.box(1);
-        const bool ax = aabb_axis(w0.x, w0.y, r.o.x, inv.x, t0, t1);
-        const bool ay = aabb_axis(w0.z, w0.w, r.o.y, inv.y, t0, t1);
-        const bool az = aabb_axis(w1.x, w1.y, r.o.z, inv.z, t0, t1);
-        if (!(ax & ay & az)) op = reinterpret_cast<const float4 *>(reinterpret_cast<const char *>(self) + (int)arg);
       } break;
       case rtd::K_TRANSLATION:
         cnt.translation();
@@ -688,7 +692,9 @@ __device__ __forceinline__ bool trace_fast(const Scene &sc, const Ray &r, float 
   for (;;) {
     const uint32_t kind = rtd::ref_kind(cur);
     const uint32_t idx = rtd::ref_index(cur);
-    if (kind == rtd::K_BVH) {
+    // a range test on the link itself: the compiler lowers a chain of tests on `kind` to a search tree that reaches the
+    // node case, nine visits in ten, through three compare-and-branch pairs
+    if (cur - (rtd::K_BVH << rtd::KIND_SHIFT) < (1u << rtd::KIND_SHIFT)) {
       const float4 n0 = ldg4(sc.fast_nodes + 4 * idx);
       const float4 n1 = ldg4(sc.fast_nodes + 4 * idx + 1);
       const float4 n2 = ldg4(sc.fast_nodes + 4 * idx + 2);
