@@ -104,7 +104,7 @@ EXPORTS = [
     "rt_render_params_from_camera", "rt_render_device", "rt_render_device_static", "rt_resolve_device", "rt_render", "rt_synchronize",
     "rt_render_state_save", "rt_render_state_load",
     "rt_group_create", "rt_group_destroy", "rt_group_size", "rt_group_context", "rt_group_last_error", "rt_group_render_world",
-    "rt_scene_pack_info", "rt_render_plan_query", "rt_scene_program", "rt_render_world", "rt_probe_trace", "rt_probe_scatter", "rt_probe_texture", "rt_probe_xorwow",
+    "rt_scene_pack_info", "rt_render_plan_query", "rt_scene_program", "rt_scene_linear_image", "rt_render_world", "rt_probe_trace", "rt_probe_scatter", "rt_probe_texture", "rt_probe_xorwow",
     # rt_scene.h
     "rt_world_init", "rt_world_free", "rt_mat_lambert_solid", "rt_mat_light_solid", "rt_mat_lambert_image",
     "rt_mat_lambert_image_pixels",
@@ -143,6 +143,7 @@ def lib():
         L.rt_scene_pack_info.argtypes = [C.POINTER(SceneDesc), C.c_uint32, C.c_uint32, C.c_uint32, C.POINTER(PackInfo)]
         L.rt_render_plan_query.argtypes = [C.POINTER(PackInfo), C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(RenderPlan)]
         L.rt_scene_program.argtypes = [C.POINTER(SceneDesc), C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]
+        L.rt_scene_linear_image.argtypes = [C.POINTER(SceneDesc), C.c_uint32, C.c_void_p, C.c_uint32, C.POINTER(C.c_uint32)]
         L.rt_render_state_save.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
         L.rt_render_state_load.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.c_uint64]
         L.rt_render_world.argtypes = [C.c_void_p, C.POINTER(World), C.POINTER(RenderSettings), C.c_uint32, C.c_void_p,
@@ -300,6 +301,16 @@ class HostScene:
         if n.value:
             _check(lib().rt_scene_program(C.byref(d), ops.ctypes.data, n.value, C.byref(n)))
         return ops
+
+    def linear_image(self, axis_quads=True):
+        """The image of the linear program as the kernels walk it (host only): uint32 view, shape (16-byte words, 4)."""
+        d = self.desc()
+        n = C.c_uint32(0)
+        _check(lib().rt_scene_linear_image(C.byref(d), 1 if axis_quads else 0, None, 0, C.byref(n)))
+        words = np.zeros((n.value, 4), dtype=np.uint32)
+        if n.value:
+            _check(lib().rt_scene_linear_image(C.byref(d), 1 if axis_quads else 0, words.ctypes.data, n.value, C.byref(n)))
+        return words
 
     def close(self):
         if self.world.hittables:

@@ -619,6 +619,18 @@ int rt_scene_program(const rt_scene_desc *scene, float *ops8_out, uint32_t capac
   return RT_OK;
 }
 
+int rt_scene_linear_image(const rt_scene_desc *scene, uint32_t axis_quads, float *float4_out, uint32_t capacity_float4, uint32_t *n_float4_out) {
+  if (!scene || !n_float4_out || (capacity_float4 > 0 && !float4_out)) return fail(nullptr, RT_ERR_INVALID, "rt_scene_linear_image: NULL argument");
+  rtp::PackedScene p;
+  const int rc = rtp::pack_scene(*scene, RT_TRAVERSAL_AUTO, p);
+  if (rc != RT_OK) return fail(nullptr, rc, p.error);
+  std::vector<float4> image;
+  if (kernel_mode(p) == 3) rtp::build_linear_image(p, axis_quads != 0, image);
+  *n_float4_out = (uint32_t)image.size();
+  if (!image.empty() && capacity_float4 > 0) memcpy(float4_out, image.data(), sizeof(float4) * (size_t)std::min<uint32_t>((uint32_t)image.size(), capacity_float4));
+  return RT_OK;
+}
+
 int rt_probe_xorwow(rt_context *ctx, uint64_t seed, uint64_t first_subsequence, uint64_t n, uint32_t *states6_out) {
   if (!ctx || !states6_out) return fail(ctx, RT_ERR_INVALID, "rt_probe_xorwow: NULL argument");
   RT_CUDA(ctx, cudaSetDevice(ctx->device));

@@ -238,6 +238,16 @@ int rt_render_plan_query(const rt_pack_info *scene, int32_t img_width, int32_t r
  * two words of an op are raw 32-bit integers.  *n_ops_out = ops of the program (0: the scene has none); at most
  * capacity_ops ops are written to ops8_out (may be NULL with capacity 0). */
 int rt_scene_program(const rt_scene_desc *scene, float *ops8_out, uint32_t capacity_ops, uint32_t *n_ops_out);
+/* translate(rotate(x)) is one op each way (flag 0x200): way in {offset.xyz,0, sin,cos,0, 4 | 0x200}, way out
+ * {sin,cos,offset.x,offset.y, offset.z,0,0, 7 | 0x200}.
+ *
+ * The IMAGE of that program as the kernels walk it (host only; what rt_scene_upload copies to the device and every block
+ * to shared memory): the ops with their indices turned into byte offsets relative to the op -- a box {.., .., byte offset
+ * to the op a missed box continues at, 1 | 0x10}, a primitive {.., byte offset to its record, 0, index, kind | 0x8 for a
+ * quad / triangle} -- then the end op {0, 0,0,0, 0 | 0x400}, then 4 x 16 bytes per quad / triangle ({n,d} {q,w.x} {v,w.y}
+ * {u,w.z}, or with axis_quads != 0 on a scene whose rt_pack_info says program_axis_quads the reduced {n,d} {q,w.k}
+ * {S_alpha,0} {S_beta,0}) and 2 x 16 bytes per sphere.  *n_float4_out = size of the image in 16-byte words (0: no program). */
+int rt_scene_linear_image(const rt_scene_desc *scene, uint32_t axis_quads, float *float4_out, uint32_t capacity_float4, uint32_t *n_float4_out);
 
 #ifdef __cplusplus
 }

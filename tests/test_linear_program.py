@@ -153,3 +153,106 @@ def test_wrapper_inside_a_wrapper_of_its_own_kind_keeps_the_stack_walk(product_l
     n = C.c_uint32(7)
     assert product_lib.lib().rt_scene_program(C.byref(d), None, 0, C.byref(n)) == 0 and n.value == 0
     hs.close()
+
+
+@pytest.mark.parametrize("sid", list(range(20)))
+def test_image_of_the_program_is_the_program_in_relative_addresses(product_lib, sid):
+    """What the kernels walk (rt_scene_linear_image, built at upload): the program's ops with their indices turned into byte
+    offsets relative to the op, an end op, then the records the ops test -- so that the walk needs no base address.  Every
+    offset must land where the index pointed; the two frequent kinds carry their flag bit."""
+    hs = product_lib.HostScene(sid)
+    ops = hs.program()
+    for axis in (False, True):
+        img = hs.linear_image(axis)
+        if len(ops) == 0:
+            assert len(img) == 0
+            continue
+        info = hs.pack_info()
+        n = len(ops)
+        assert len(img) == 2 * (n + 1) + 4 * info.planars + 2 * info.spheres
+        planar0, sphere0 = 2 * (n + 1), 2 * (n + 1) + 4 * info.planars            # first 16-byte word of the record arrays
+        iops = img[:2 * (n + 1)].reshape(n + 1, 8)
+        for i in range(n):
+            code, kind = int(iops[i, 7]), int(ops[i, 7]) & 7
+            assert code & ~0x18 == int(ops[i, 7])                                  # same code, plus the flag bits
+            assert bool(code & 0x8) == (kind in (TRIANGLE, QUAD)) and bool(code & 0x10) == (kind == BVH)
+            assert np.array_equal(iops[i, :4], ops[i, :4])
+            if kind == BVH:
+                delta = int(iops[i, 6].astype(np.int32))
+                assert delta % 32 == 0 and i + delta // 32 == int(ops[i, 6]) and delta > 0
+                assert np.array_equal(iops[i, 4:6], ops[i, 4:6])
+            elif kind in (TRIANGLE, QUAD, SPHERE):
+                assert iops[i, 6] == ops[i, 6]                                      # the primitive index stays (it names the material)
+                delta = int(iops[i, 4].astype(np.int32))
+                assert delta % 16 == 0
+                word = 2 * i + delta // 16
+                if kind == SPHERE:
+                    assert word == sphere0 + 2 * int(ops[i, 6])
+                else:
+                    assert word == planar0 + 4 * int(ops[i, 6])
+                    assert np.array_equal(img[word], iops[i, :4])                  # {n, d}: the first word of the record rides in the op
+            else:
+                assert np.array_equal(iops[i, 4:7], ops[i, 4:7])                   # wrappers: untouched
+        assert int(iops[n, 7]) == 0x400 and not iops[n, :7].any()                   # the end op
+        if axis and info.program_axis_quads:                                        # reduced records: one non-zero in each S
+            rec = img[planar0:planar0 + 4 * info.planars].view(np.float32).reshape(info.planars, 4, 4)
+            assert (np.count_nonzero(rec[:, 2, :3], axis=1) == 1).all() and (np.count_nonzero(rec[:, 3, :3], axis=1) == 1).all()
+            assert (rec[:, 2, 3] == 0).all() and (rec[:, 3, 3] == 0).all()
+            general = hs.linear_image(False)[planar0:planar0 + 4 * info.planars].view(np.float32).reshape(info.planars, 4, 4)
+            assert np.array_equal(rec[:, 0], general[:, 0]) and np.array_equal(rec[:, 1, :3], general[:, 1, :3])
+        elif not axis:
+            pass
+    hs.close()
+
+
+def _f32(x):
+    return np.asarray(x, dtype=np.float32)
+
+
+def _fma(a, b, c):
+    """float32 fma through float64: the product of two float32 is exact in float64; adding an exact zero (all this test
+    needs) is exact as well"""
+    return _f32(_f32(a).astype(np.float64) * _f32(b).astype(np.float64) + _f32(c).astype(np.float64))
+
+
+def _mul(a, b):
+    return _f32(_f32(a).astype(np.float64) * _f32(b).astype(np.float64))
+
+
+def _dot_yfirst(a, b):                                     # rt_math.cuh: fma(z,z', fma(x,x', y*y'))
+    return _fma(a[..., 2], b[..., 2], _fma(a[..., 0], b[..., 0], _mul(a[..., 1], b[..., 1])))
+
+
+def _cross(a, b):                                          # rt_math.cuh: fma(a, b, -(c*d)) per component
+    return np.stack([_fma(a[..., 1], b[..., 2], -_mul(a[..., 2], b[..., 1])), _fma(a[..., 2], b[..., 0], -_mul(a[..., 0], b[..., 2])),
+                     _fma(a[..., 0], b[..., 1], -_mul(a[..., 1], b[..., 0]))], axis=-1)
+
+
+def test_reduced_inside_test_of_axis_aligned_quads_has_the_general_roundings(product_lib):
+    """Cornell box: alpha / beta of the reduced records (w.k * dot(pl, S)) against the reference's formula
+    (dot(w, cross(pl, v)), dot(w, cross(u, pl)), rt.cu:1069-1070) with the kernels' fma chains, bit for bit, on random
+    points around every quad -- the terms the reduced form leaves out are products with an exact zero."""
+    hs = product_lib.HostScene(1)
+    info = hs.pack_info()
+    assert info.program_axis_quads == 1
+    n = info.program_ops
+    first = 2 * (n + 1)
+    gen = hs.linear_image(False)[first:first + 4 * info.planars].view(np.float32).reshape(info.planars, 4, 4)
+    red = hs.linear_image(True)[first:first + 4 * info.planars].view(np.float32).reshape(info.planars, 4, 4)
+    rng = np.random.default_rng(5)
+    for k in range(info.planars):
+        q, w = gen[k, 1, :3], np.array([gen[k, 1, 3], gen[k, 2, 3], gen[k, 3, 3]], dtype=np.float32)
+        v, u = gen[k, 2, :3], gen[k, 3, :3]
+        pts = _f32(q + rng.uniform(-1.2, 1.2, (4000, 1)) * u + rng.uniform(-1.2, 1.2, (4000, 1)) * v + rng.normal(0, 1e-3, (4000, 3)))
+        pl = _f32(pts - q)
+        alpha = _dot_yfirst(np.broadcast_to(w, pl.shape), _cross(pl, np.broadcast_to(v, pl.shape)))
+        beta = _dot_yfirst(np.broadcast_to(w, pl.shape), _cross(np.broadcast_to(u, pl.shape), pl))
+        wk = red[k, 1, 3]
+        alpha_r = _mul(wk, _dot_yfirst(pl, np.broadcast_to(red[k, 2, :3], pl.shape)))
+        beta_r = _mul(wk, _dot_yfirst(pl, np.broadcast_to(red[k, 3, :3], pl.shape)))
+        # identical bits, up to the sign of an exact zero (which no comparison of the inside test sees)
+        for a, b in ((alpha, alpha_r), (beta, beta_r)):
+            same = (a.view(np.uint32) == b.view(np.uint32)) | ((a == 0) & (b == 0))
+            assert same.all(), (k, a[~same][:3], b[~same][:3])
+        assert ((alpha >= 0) & (alpha <= 1)).any() and ((alpha < 0) | (alpha > 1)).any()      # the sample straddles the quad
+    hs.close()
